@@ -1,0 +1,152 @@
+// afe_fbank.cu -- C ABI entry point of the batched fbank featuriser.
+#include <algorithm>
+
+#include "afe_ctx.h"
+#include "afe_fbank_kernels.h"
+
+using namespace afe;
+
+namespace {
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// workspace layout (device): [descriptors][partials: ntiles*80*2 f64][stats: B*80*2 f32]
+struct FbankLayout {
+  int B = 0;
+  long ntiles = 0;
+  size_t off_wave = 0, off_len = 0, off_frames = 0, off_prefix = 0, off_row = 0, off_tp = 0, desc_bytes = 0;
+  size_t off_partials = 0, off_stats = 0, total = 0;
+};
+
+FbankLayout fbank_layout(const int64_t* lengths, int B) {
+  FbankLayout l;
+  l.B = B;
+  for (int b = 0; b < B; ++b) {
+    const int64_t T = afe_fbank_num_frames(lengths[b]);
+    l.ntiles += (long)((T + kTileFrames - 1) / kTileFrames);
+  }
+  size_t o = 0;
+  l.off_wave = o;   o = align_up(o + sizeof(void*) * (size_t)B, 16);
+  l.off_len = o;    o = align_up(o + sizeof(int64_t) * (size_t)B, 16);
+  l.off_prefix = o; o = align_up(o + sizeof(int64_t) * ((size_t)B + 1), 16);
+  l.off_row = o;    o = align_up(o + sizeof(int64_t) * (size_t)B, 16);
+  l.off_frames = o; o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
+  l.off_tp = o;     o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
+  l.desc_bytes = o;
+  l.off_partials = align_up(o, 256);
+  l.off_stats = align_up(l.off_partials + sizeof(double) * 2 * kMel * (size_t)l.ntiles, 256);
+  l.total = align_up(l.off_stats + sizeof(float) * 2 * kMel * (size_t)B, 256);
+  return l;
+}
+
+template <typename T>
+int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, double* partials,
+              const T* window, const T* tw) {
+  FbankKernel<T> k;
+  k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
+  k.mel_start = ctx->d_mel_start; k.mel_count = ctx->d_mel_count; k.mel_offset = ctx->d_mel_offset;
+  k.mel_w = ctx->d_mel_w; k.log_floor = ctx->log_floor;
+  return afe_launch(k, FbankSmem<T>::kBytes, ctx->num_sms, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t afe_fbank_workspace_bytes(const int64_t* h_lengths, int batch) {
+  if (!h_lengths || batch <= 0) return 256;
+  return fbank_layout(h_lengths, batch).total;
+}
+
+int afe_fbank_layout(const int64_t* h_lengths, int batch, int group_size, int64_t* h_group_tp, int64_t* total_rows) {
+  if (batch < 0 || (batch > 0 && !h_lengths)) return fail(AFE_ERR_INVALID, "afe_fbank_layout: bad arguments");
+  const int G = group_size > 0 ? group_size : (batch > 0 ? batch : 1);
+  int64_t rows = 0;
+  for (int g0 = 0, g = 0; g0 < batch; g0 += G, ++g) {
+    const int n = std::min(G, batch - g0);
+    const int64_t tp = afe_fbank_padded_frames(h_lengths + g0, n);
+    if (h_group_tp) h_group_tp[g] = tp;
+    rows += tp * n;
+  }
+  if (total_rows) *total_rows = rows;
+  return AFE_OK;
+}
+
+int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
+                    int group_size, float padding_value, int precision, int flags, float* d_features,
+                    int32_t* d_mask, void* d_workspace, size_t workspace_bytes) {
+  if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch: bad arguments");
+  if (batch == 0) return AFE_OK;
+  if (!h_waves || !h_lengths || !d_workspace) return fail(AFE_ERR_INVALID, "afe_fbank_batch: NULL argument");
+  if (precision != AFE_PRECISION_F64 && precision != AFE_PRECISION_F32)
+    return fail(AFE_ERR_INVALID, "afe_fbank_batch: unknown precision");
+  const bool raw_only = (flags & AFE_FBANK_RAW) != 0;
+  const FbankLayout l = fbank_layout(h_lengths, batch);
+  if (workspace_bytes < l.total) return fail(AFE_ERR_WORKSPACE, "afe_fbank_batch: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int G = group_size > 0 ? group_size : batch;
+
+  // descriptors: pinned staging -> head of the workspace
+  StagingBlock* blk = ctx->staging_acquire(l.desc_bytes);
+  if (!blk) return AFE_ERR_CUDA;
+  unsigned char* h = static_cast<unsigned char*>(blk->host);
+  const float** hw = reinterpret_cast<const float**>(h + l.off_wave);
+  int64_t* hl = reinterpret_cast<int64_t*>(h + l.off_len);
+  int64_t* hp = reinterpret_cast<int64_t*>(h + l.off_prefix);
+  int64_t* hr = reinterpret_cast<int64_t*>(h + l.off_row);
+  int32_t* hf = reinterpret_cast<int32_t*>(h + l.off_frames);
+  int32_t* ht = reinterpret_cast<int32_t*>(h + l.off_tp);
+  int64_t acc = 0, rows = 0, tp_max = 0;
+  bool bad = false;
+  for (int g0 = 0; g0 < batch; g0 += G) {
+    const int n = std::min(G, batch - g0);
+    const int64_t tp = afe_fbank_padded_frames(h_lengths + g0, n);
+    tp_max = std::max(tp_max, tp);
+    for (int b = g0; b < g0 + n; ++b) {
+      const int64_t T = afe_fbank_num_frames(h_lengths[b]);
+      if (T > 0 && !h_waves[b]) bad = true;
+      hw[b] = h_waves[b]; hl[b] = h_lengths[b]; hf[b] = (int32_t)T; hp[b] = acc; hr[b] = rows; ht[b] = (int32_t)tp;
+      acc += (T + kTileFrames - 1) / kTileFrames;
+      rows += tp;
+    }
+  }
+  hp[batch] = acc;
+  if (bad || (rows > 0 && (!d_features || (!raw_only && !d_mask)))) {
+    ctx->staging_submit(blk, s);
+    return fail(AFE_ERR_INVALID, "afe_fbank_batch: NULL waveform or output");
+  }
+  unsigned char* ws = static_cast<unsigned char*>(d_workspace);
+  const int up = dev_upload_async(ws, h, l.desc_bytes, s);
+  ctx->staging_submit(blk, s);
+  if (up != 0) return AFE_ERR_CUDA;
+
+  BatchDesc d;
+  d.wave = reinterpret_cast<const float* const*>(ws + l.off_wave);
+  d.len = reinterpret_cast<const int64_t*>(ws + l.off_len);
+  d.frames = reinterpret_cast<const int32_t*>(ws + l.off_frames);
+  d.tile_prefix = reinterpret_cast<const int64_t*>(ws + l.off_prefix);
+  d.out_row = reinterpret_cast<const int64_t*>(ws + l.off_row);
+  d.tp = reinterpret_cast<const int32_t*>(ws + l.off_tp);
+  d.B = batch; d.ntiles = l.ntiles;
+  double* partials = reinterpret_cast<double*>(ws + l.off_partials);
+  float* stats = reinterpret_cast<float*>(ws + l.off_stats);
+
+  int rc = (precision == AFE_PRECISION_F64)
+               ? run_fbank<double>(ctx, s, d, d_features, partials, ctx->d_povey64, ctx->d_tw64)
+               : run_fbank<float>(ctx, s, d, d_features, partials, ctx->d_povey32, ctx->d_tw32);
+  if (rc == 0 && !raw_only && rows > 0) {
+    FbankStatsKernel sk{d, partials, stats};
+    rc = afe_launch(sk, 0, 1 << 20, s);
+    if (rc == 0) {
+      FbankNormKernel nk;
+      nk.d = d; nk.feat = d_features; nk.mask = d_mask; nk.stats = stats;
+      nk.padding_value = padding_value;
+      nk.items_per_utt = (long)((tp_max * kMel + FbankNormKernel::kItemFloats - 1) / FbankNormKernel::kItemFloats);
+      rc = afe_launch(nk, 0, ctx->num_sms * 8, s);
+    }
+  }
+  if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_fbank_batch: launch failed: ") + dev_last_error_string());
+  return AFE_OK;
+}
+
+}  // extern "C"

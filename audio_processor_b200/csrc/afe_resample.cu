@@ -1,0 +1,81 @@
+// afe_resample.cu -- C ABI entry points for resampling and the stereo mix.
+#include "afe_ctx.h"
+#include "afe_resample_kernels.h"
+
+using namespace afe;
+
+namespace afe {
+// mixed = (row0 + row1) * 0.5 when no resampling is needed (sample_rate == target)
+struct MixKernel {
+  static constexpr int kThreads = 256;
+  static constexpr int kMinBlocks = 8;
+  static constexpr int kPhases = 1;
+  static constexpr int kItem = 4096;
+  const float* in; float* mixed; int64_t L;
+  AFE_HD long num_items() const { return (long)((L + kItem - 1) / kItem); }
+  AFE_HD void phase(int, long item, unsigned char*, int tid) const {
+    for (int v = tid; v < kItem; v += kThreads) {
+      const int64_t i = item * kItem + v;
+      if (i < L) mixed[i] = (in[i] + in[L + i]) * 0.5f;
+    }
+  }
+};
+}  // namespace afe
+
+extern "C" {
+
+int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed) {
+  if (!ctx || !d_in || !d_mixed || length < 0) return fail(AFE_ERR_INVALID, "afe_mix_stereo: bad arguments");
+  MixKernel k{d_in, d_mixed, length};
+  if (afe_launch(k, 0, ctx->num_sms * 8, (cudaStream_t)stream) != 0) return fail(AFE_ERR_CUDA, "afe_mix_stereo: launch failed");
+  return AFE_OK;
+}
+
+int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_t length, int orig_hz,
+                 int new_hz, float* d_out, float* d_mixed, int64_t out_length) {
+  if (!ctx || !d_in || !d_out || rows <= 0 || length < 0 || orig_hz <= 0 || new_hz <= 0)
+    return fail(AFE_ERR_INVALID, "afe_resample: bad arguments");
+  if (orig_hz == new_hz) return fail(AFE_ERR_INVALID, "afe_resample: equal rates need no resampling");
+  if (out_length != resampled_length(length, orig_hz, new_hz))
+    return fail(AFE_ERR_INVALID, "afe_resample: out_length must equal ceil(new*L/orig)");
+  if (d_mixed && rows != 2) return fail(AFE_ERR_INVALID, "afe_resample: mixed output needs exactly 2 rows");
+  if (length == 0) return AFE_OK;
+  const DeviceTaps* dt = ctx->get_taps(orig_hz, new_hz);
+  if (!dt) return AFE_ERR_CUDA;
+  const ResampleTaps& t = dt->host;
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc;
+  if (t.O == 1 && t.N == 2 && t.K == 15) {
+    const long ipr = (long)((length + 1023) / 1024);
+    if (rows == 2 && d_mixed) {
+      Upsample2xKernel<true> k;
+      k.in = d_in; k.out = d_out; k.mixed = d_mixed; k.L = length; k.rows = 2; k.items_per_row = ipr;
+      for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
+      rc = afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * 8, s);
+    } else {
+      Upsample2xKernel<false> k;
+      k.in = d_in; k.out = d_out; k.mixed = nullptr; k.L = length; k.rows = rows; k.items_per_row = ipr;
+      for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
+      rc = afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * 8, s);
+    }
+  } else {
+    PolyphaseKernel k;
+    k.in = d_in; k.out = d_out; k.tapsT = dt->d_tapsT; k.L = length; k.out_len = out_length;
+    k.rows = rows; k.O = t.O; k.N = t.N; k.K = t.K; k.width = t.width;
+    k.jgroups = (t.N + 31) / 32;
+    const int64_t periods = (out_length + t.N - 1) / t.N;
+    k.ntiles = (long)((periods + PolyphaseKernel::kPeriods - 1) / PolyphaseKernel::kPeriods);
+    const size_t smem = k.smem_bytes();
+    if (smem > 200 * 1024) return fail(AFE_ERR_UNSUPPORTED, "afe_resample: tap tile exceeds shared memory for this rate pair");
+    rc = afe_launch(k, smem, ctx->num_sms * 2, s);
+    if (rc == 0 && d_mixed) {
+      // generic path: mix the two resampled rows afterwards
+      MixKernel m{d_out, d_mixed, out_length};
+      rc = afe_launch(m, 0, ctx->num_sms * 8, s);
+    }
+  }
+  if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_resample: launch failed: ") + dev_last_error_string());
+  return AFE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,176 @@
+// afe_runtime.cu -- memory / error plumbing and the afe_ctx lifecycle.
+// Compiled by nvcc (product) and by g++ -x c++ -DAFE_EMULATE (test-only emulation).
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+
+#include "afe_ctx.h"
+
+namespace afe {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+int fail(int code, const std::string& msg) { set_error(msg); return code; }
+void note_error(const char* what, const char* detail) { set_error(std::string(what) + ": " + detail); }
+
+#if AFE_CUDA
+static int cuda_fail(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return 0;
+  set_error(std::string(what) + ": " + cudaGetErrorString(e));
+  return -1;
+}
+int dev_set(int device) { return cuda_fail(cudaSetDevice(device), "cudaSetDevice"); }
+void* dev_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cuda_fail(cudaMalloc(&p, bytes), "cudaMalloc") != 0) return nullptr;
+  return p;
+}
+void dev_free(void* p) { if (p) cudaFree(p); }
+int dev_upload(void* dst, const void* src, size_t bytes) {
+  return cuda_fail(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice), "cudaMemcpy H2D");
+}
+int dev_upload_async(void* dst, const void* src, size_t bytes, cudaStream_t s) {
+  return cuda_fail(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s), "cudaMemcpyAsync H2D");
+}
+int dev_memset_async(void* dst, int v, size_t bytes, cudaStream_t s) {
+  return cuda_fail(cudaMemsetAsync(dst, v, bytes, s), "cudaMemsetAsync");
+}
+void* host_pinned_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cuda_fail(cudaMallocHost(&p, bytes), "cudaMallocHost") != 0) return nullptr;
+  return p;
+}
+void host_pinned_free(void* p) { if (p) cudaFreeHost(p); }
+int dev_check_last() { return cuda_fail(cudaGetLastError(), "kernel launch"); }
+#else
+int dev_set(int) { return 0; }
+void* dev_alloc(size_t bytes) { return std::calloc(1, bytes ? bytes : 1); }
+void dev_free(void* p) { std::free(p); }
+int dev_upload(void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); return 0; }
+int dev_upload_async(void* dst, const void* src, size_t bytes, cudaStream_t) { std::memcpy(dst, src, bytes); return 0; }
+int dev_memset_async(void* dst, int v, size_t bytes, cudaStream_t) { std::memset(dst, v, bytes); return 0; }
+void* host_pinned_alloc(size_t bytes) { return std::malloc(bytes ? bytes : 1); }
+void host_pinned_free(void* p) { std::free(p); }
+int dev_check_last() { return 0; }
+#endif
+const char* dev_last_error_string() { return g_last_error.c_str(); }
+
+}  // namespace afe
+
+using namespace afe;
+
+afe::StagingBlock* afe_ctx::staging_acquire(size_t bytes) {
+  std::lock_guard<std::mutex> lock(mu);
+  for (auto& b : staging) {
+    if (b.cap < bytes) continue;
+    if (b.in_flight) {
+#if AFE_CUDA
+      if (cudaEventQuery((cudaEvent_t)b.event) != cudaSuccess) continue;
+#endif
+      b.in_flight = false;
+    }
+    b.in_flight = true;                           // reserved by this call
+    return &b;
+  }
+  if (staging.capacity() < 256) staging.reserve(256);     // keep pointers stable
+  if (staging.size() >= 256) { set_error("staging pool exhausted"); return nullptr; }
+  StagingBlock nb;
+  nb.cap = bytes < 65536 ? 65536 : bytes;
+  nb.host = host_pinned_alloc(nb.cap);
+  if (!nb.host) return nullptr;
+#if AFE_CUDA
+  cudaEvent_t ev;
+  if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { host_pinned_free(nb.host); return nullptr; }
+  nb.event = ev;
+#endif
+  nb.in_flight = true;
+  staging.push_back(nb);
+  return &staging.back();
+}
+
+void afe_ctx::staging_submit(afe::StagingBlock* blk, cudaStream_t stream) {
+#if AFE_CUDA
+  cudaEventRecord((cudaEvent_t)blk->event, stream);
+#else
+  (void)stream;
+  std::lock_guard<std::mutex> lock(mu);
+  blk->in_flight = false;
+#endif
+}
+
+const afe::DeviceTaps* afe_ctx::get_taps(int orig_hz, int new_hz) {
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair(orig_hz, new_hz);
+  auto it = taps.find(key);
+  if (it != taps.end()) return &it->second;
+  DeviceTaps dt;
+  dt.host = make_resample_taps(orig_hz, new_hz);
+  dt.d_tapsT = upload(dt.host.tapsT);
+  if (!dt.d_tapsT) return nullptr;
+  return &taps.emplace(key, std::move(dt)).first->second;
+}
+
+extern "C" {
+
+const char* afe_version(void) { return "afe-b200 0.1.0"; }
+int afe_backend(void) { return AFE_CUDA ? 1 : 2; }
+const char* afe_last_error(void) { return dev_last_error_string(); }
+int afe_num_sms(const afe_ctx* ctx) { return ctx ? ctx->num_sms : 0; }
+
+int afe_create(int device, afe_ctx** out) {
+  if (!out) return fail(AFE_ERR_INVALID, "afe_create: out is NULL");
+  *out = nullptr;
+#if AFE_CUDA
+  int prev = 0;
+  cudaGetDevice(&prev);
+  if (dev_set(device) != 0) return AFE_ERR_CUDA;
+#endif
+  afe_ctx* c = new afe_ctx();
+  c->device = device;
+#if AFE_CUDA
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0) c->num_sms = sms;
+#endif
+  bool ok = true;
+  {
+    std::vector<double> w = make_povey_window();
+    std::vector<double> w64(w.size()); std::vector<float> w32(w.size());
+    for (size_t i = 0; i < w.size(); ++i) { w64[i] = w[i] * 16384.0; w32[i] = (float)(w[i] * 16384.0); }   // 32768 / 2
+    ok = ok && (c->d_povey64 = c->upload(w64)) && (c->d_povey32 = c->upload(w32));
+    std::vector<double> tw = make_twiddle512();
+    std::vector<float> tw32(tw.begin(), tw.end());
+    ok = ok && (c->d_tw64 = c->upload(tw)) && (c->d_tw32 = c->upload(tw32));
+    SparseBank mel = make_kaldi_mel_bank();
+    ok = ok && (c->d_mel_start = c->upload(mel.start)) && (c->d_mel_count = c->upload(mel.count)) &&
+         (c->d_mel_offset = c->upload(mel.offset)) && (c->d_mel_w = c->upload(mel.w));
+    std::vector<double> hn = make_hann_periodic();
+    std::vector<float> hn32(hn.size());
+    for (size_t i = 0; i < hn.size(); ++i) hn32[i] = (float)(hn[i] * 0.5);
+    ok = ok && (c->d_hann32 = c->upload(hn32));
+    SparseBank htk = make_htk_mel_bank();
+    ok = ok && (c->d_htk_start = c->upload(htk.start)) && (c->d_htk_count = c->upload(htk.count)) &&
+         (c->d_htk_offset = c->upload(htk.offset)) && (c->d_htk_w = c->upload(htk.w));
+    ok = ok && (c->d_dct = c->upload(make_dct_matrix()));
+    c->log_floor = (float)std::log((double)kMelFloor);
+  }
+#if AFE_CUDA
+  cudaSetDevice(prev);
+#endif
+  if (!ok) { afe_destroy(c); return AFE_ERR_CUDA; }
+  *out = c;
+  return AFE_OK;
+}
+
+void afe_destroy(afe_ctx* c) {
+  if (!c) return;
+  for (void* p : c->owned) dev_free(p);
+  for (auto& b : c->staging) {
+#if AFE_CUDA
+    if (b.event) cudaEventDestroy((cudaEvent_t)b.event);
+#endif
+    host_pinned_free(b.host);
+  }
+  delete c;
+}
+
+}  // extern "C"

@@ -1,0 +1,178 @@
+"""Device runtime: one ``Frontend`` per CUDA device, a thin typed layer over the C ABI.
+
+PyTorch is plumbing here (device memory, the caching allocator, the current stream); all
+arithmetic happens in ``libafe.so``.  Every method enqueues on ``torch.cuda.current_stream``
+and never synchronises unless it has to hand Python scalars back.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import _native
+
+Wave = Union[np.ndarray, torch.Tensor]
+
+_frontends: Dict[int, "Frontend"] = {}
+_frontends_lock = threading.Lock()
+
+
+def get_frontend(device: Union[int, str, torch.device, None] = None) -> "Frontend":
+    """The per-device singleton.  Raises if CUDA or the native library is unavailable."""
+    if not torch.cuda.is_available():
+        raise _native.AfeLibraryError("audio_processor_b200 needs a CUDA device (no CPU fallback)")
+    if device is None:
+        idx = torch.cuda.current_device()
+    else:
+        dev = torch.device(device) if not isinstance(device, int) else torch.device("cuda", device)
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    with _frontends_lock:
+        fe = _frontends.get(idx)
+        if fe is None:
+            fe = Frontend(idx)
+            _frontends[idx] = fe
+        return fe
+
+
+class Frontend:
+    def __init__(self, device_index: int):
+        self.lib = _native.load()
+        self.device = torch.device("cuda", device_index)
+        self.ctx = self.lib.create(device_index)
+        self.num_sms = int(self.lib.afe_num_sms(self.ctx))
+        self._tls = threading.local()
+
+    # ------------------------------------------------------------------ helpers
+    def _stream(self) -> C.c_void_p:
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _workspace(self, nbytes: int) -> torch.Tensor:
+        ws = getattr(self._tls, "ws", None)
+        if ws is None or ws.numel() < nbytes:
+            ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
+            self._tls.ws = ws
+        return ws
+
+    def _to_device_1d(self, waves: Sequence[Wave]) -> Tuple[List[torch.Tensor], List[int]]:
+        """Mono float32 device views of every waveform; host inputs share ONE pinned staging
+        buffer and ONE H2D copy (offsets rounded to 4 floats so rows stay 16-byte aligned)."""
+        out: List[Optional[torch.Tensor]] = [None] * len(waves)
+        host_idx, host_arr = [], []
+        for i, w in enumerate(waves):
+            if isinstance(w, torch.Tensor):
+                t = w.detach()
+                if t.dim() == 2:
+                    t = t[0]                       # stereo arrays: channel 0 only (reference :121-122)
+                t = t.reshape(-1)
+                if t.is_cuda:
+                    out[i] = t.to(device=self.device, dtype=torch.float32).contiguous()
+                    continue
+                w = t.to(torch.float32).contiguous().numpy()
+            a = np.asarray(w)
+            if a.ndim == 2:
+                a = a[0]
+            host_idx.append(i)
+            host_arr.append(np.ascontiguousarray(a.reshape(-1), dtype=np.float32))
+        if host_idx:
+            offs, total = [], 0
+            for a in host_arr:
+                offs.append(total)
+                total += (a.size + 3) // 4 * 4
+            pinned = torch.empty(max(total, 1), dtype=torch.float32, pin_memory=True)
+            pv = pinned.numpy()
+            for a, o in zip(host_arr, offs):
+                pv[o:o + a.size] = a
+            dev = pinned.to(self.device, non_blocking=True)
+            self._tls.last_pinned = pinned          # keep alive until the next call on this thread
+            for i, a, o in zip(host_idx, host_arr, offs):
+                out[i] = dev[o:o + a.size]
+        lens = [int(t.numel()) for t in out]
+        return out, lens  # type: ignore[return-value]
+
+    # ------------------------------------------------------------------ resample
+    def resampled_length(self, length: int, orig: int, new: int) -> int:
+        return int(self.lib.afe_resampled_length(int(length), int(orig), int(new)))
+
+    def resample(self, x: torch.Tensor, orig: int, new: int, want_mixed: bool = False):
+        """``torchaudio.transforms.Resample(orig, new)(x)`` on a (..., L) float32 CUDA tensor."""
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        lead, L = x.shape[:-1], int(x.shape[-1])
+        rows = int(np.prod(lead)) if lead else 1
+        Lo = self.resampled_length(L, orig, new)
+        out = torch.empty((rows, Lo), dtype=torch.float32, device=self.device)
+        mixed = torch.empty((1, Lo), dtype=torch.float32, device=self.device) if want_mixed else None
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_resample(
+                self.ctx, self._stream(), C.c_void_p(x.data_ptr()), rows, L, int(orig), int(new),
+                C.c_void_p(out.data_ptr()), C.c_void_p(mixed.data_ptr()) if want_mixed else None, Lo))
+        out = out.reshape(tuple(lead) + (Lo,))
+        return (out, mixed) if want_mixed else out
+
+    def mix_stereo(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        L = int(x.shape[-1])
+        mixed = torch.empty((1, L), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_mix_stereo(self.ctx, self._stream(), C.c_void_p(x.data_ptr()), L,
+                                                   C.c_void_p(mixed.data_ptr())))
+        return mixed
+
+    # ------------------------------------------------------------------ fbank
+    def fbank(self, waves: Sequence[Wave], padding_value: float = 0.0, precision: int = _native.PRECISION_F64,
+              raw: bool = False, group_size: int = 0):
+        """One ``processor(...)`` call: (input_features (B, Tp/2, 160) float32, attention_mask
+        (B, Tp/2) int32) on the device.  With ``group_size`` > 0 several processor() calls are
+        featurised in one launch and a list of (features, mask) per group is returned."""
+        dev_waves, lens = self._to_device_1d(waves)
+        B = len(dev_waves)
+        G = int(group_size) if group_size and group_size > 0 else 0
+        if B == 0:
+            empty = (torch.empty((0, 0, 160), dtype=torch.float32, device=self.device),
+                     torch.empty((0, 0), dtype=torch.int32, device=self.device))
+            return [] if G else empty
+        lens_c = _native.i64_array(lens)
+        ng = (B + G - 1) // G if G else 1
+        tps = (C.c_int64 * ng)()
+        rows = C.c_int64()
+        self.lib.check(self.lib.afe_fbank_layout(lens_c, B, G, tps, C.byref(rows)))
+        half = rows.value // 2
+        feat = torch.empty((half, 160), dtype=torch.float32, device=self.device)
+        mask = torch.empty((half,), dtype=torch.int32, device=self.device)
+        ws = self._workspace(int(self.lib.afe_fbank_workspace_bytes(lens_c, B)))
+        ptrs = _native.ptr_array([t.data_ptr() if t.numel() else 0 for t in dev_waves])
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_fbank_batch(
+                self.ctx, self._stream(), ptrs, lens_c, B, G, float(padding_value), int(precision),
+                _native.FBANK_RAW if raw else 0, C.c_void_p(feat.data_ptr()), C.c_void_p(mask.data_ptr()),
+                C.c_void_p(ws.data_ptr()), ws.numel()))
+        self._tls.keep = dev_waves                  # stream-ordered lifetime of the staged inputs
+        out, r = [], 0
+        for g in range(ng):
+            n = min(G, B - g * G) if G else B
+            h = int(tps[g]) // 2
+            out.append((feat[r:r + n * h].view(n, h, 160), mask[r:r + n * h].view(n, h)))
+            r += n * h
+        return out if G else out[0]
+
+    # ------------------------------------------------------------------ acoustic
+    def acoustic(self, waves: Sequence[Wave], sample_rate: int = 16000) -> Tuple[torch.Tensor, torch.Tensor]:
+        """((B, 38) float32 feature rows, (B,) int32 status) on the device; see afe.h."""
+        dev_waves, lens = self._to_device_1d(waves)
+        B = len(dev_waves)
+        out = torch.empty((B, 38), dtype=torch.float32, device=self.device)
+        status = torch.empty((B,), dtype=torch.int32, device=self.device)
+        if B == 0:
+            return out, status
+        lens_c = _native.i64_array(lens)
+        ws = self._workspace(int(self.lib.afe_acoustic_workspace_bytes(lens_c, B)))
+        ptrs = _native.ptr_array([t.data_ptr() if t.numel() else 0 for t in dev_waves])
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_acoustic_batch(
+                self.ctx, self._stream(), ptrs, lens_c, B, int(sample_rate), C.c_void_p(out.data_ptr()),
+                C.c_void_p(status.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel()))
+        self._tls.keep = dev_waves
+        return out, status

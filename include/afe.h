@@ -1,0 +1,119 @@
+/* afe.h -- C ABI of the B200 audio front end (libafe.so).
+ *
+ * Drop-in boundary for the waveform hot path of jaratM/audio_processor.  The reference is
+ * pure Python with no FFI of its own; each entry point below names
+ * the reference call site whose arithmetic it replaces.  Conventions:
+ *   - every function returns 0 on success or a negative afe_status; afe_last_error() gives
+ *     the message of the calling thread's last failure; no C++ exception crosses the ABI;
+ *   - the caller allocates every input, output and workspace buffer; "d_" parameters are
+ *     device pointers (cudaMalloc / torch CUDA tensors), "h_" parameters are host pointers;
+ *   - work is enqueued on the caller's stream (a cudaStream_t passed as void*), nothing
+ *     synchronises; the library keeps no mutable global state and is re-entrant;
+ *   - an afe_ctx owns only immutable constant tables for one device.
+ */
+#ifndef AFE_H_
+#define AFE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct afe_ctx afe_ctx;
+
+typedef enum afe_status {
+  AFE_OK = 0,
+  AFE_ERR_INVALID = -1,      /* bad argument (also: sampling_rate != 16000 -> ValueError upstream) */
+  AFE_ERR_CUDA = -2,         /* CUDA runtime failure, message in afe_last_error */
+  AFE_ERR_WORKSPACE = -3,    /* workspace too small */
+  AFE_ERR_UNSUPPORTED = -4   /* e.g. a rate pair whose tap tile does not fit shared memory */
+} afe_status;
+
+#define AFE_FBANK_FRAME 400
+#define AFE_FBANK_HOP 160
+#define AFE_FBANK_MELS 80
+#define AFE_ACOUSTIC_FEATURES 38
+
+/* precision of the linear path (pre-emphasis .. FFT) of afe_fbank_batch */
+#define AFE_PRECISION_F64 0   /* default: matches the reference's float64 path to <= 1e-3 */
+#define AFE_PRECISION_F32 1   /* opt-in fast path, ~3e-3 worst case in empty bands */
+/* flags of afe_fbank_batch */
+#define AFE_FBANK_RAW 1       /* stop after the log-mel: no normalisation, padding or mask */
+
+/* ---- library / context ------------------------------------------------------------- */
+const char* afe_version(void);
+/* 1 = CUDA sm_100a build (the product); 2 = host emulation of the kernels (tests only) */
+int afe_backend(void);
+int afe_create(int device, afe_ctx** out);
+void afe_destroy(afe_ctx* ctx);
+const char* afe_last_error(void);
+int afe_num_sms(const afe_ctx* ctx);
+
+/* ---- host-side integer / float64 contracts (no device work) ------------------------- */
+/* ceil(new*L/orig): torchaudio _apply_sinc_resample_kernel, functional.py:1425 */
+int64_t afe_resampled_length(int64_t length, int orig_hz, int new_hz);
+/* 1 + (L - 400) / 160, 0 if L < 400: transformers audio_utils.spectrogram :778 */
+int64_t afe_fbank_num_frames(int64_t length);
+/* longest frame count rounded up to a multiple of 2: SequenceFeatureExtractor.pad,
+ * feature_extraction_seamless_m4t.py:267-275 */
+int64_t afe_fbank_padded_frames(const int64_t* h_lengths, int batch);
+/* AudioProcessor.split_audio chunk loop, services/audio_processor.py:115-158.
+ * Writes up to cap (start, end) pairs; *n receives the number of chunks. */
+int afe_chunk_table(int64_t total_samples, int64_t chunk_samples, int64_t step_samples,
+                    int64_t* h_starts, int64_t* h_ends, int cap, int* n);
+/* SpeechSegment._extract_segments, services/speech_segment.py:385-418 (float64 arithmetic,
+ * int() truncation).  intervals = n_intervals (start, end) pairs in seconds. */
+int afe_segment_table(int64_t num_samples, int sample_rate, const double* h_intervals, int n_intervals,
+                      double padding, double max_len_sec, double overlap_sec,
+                      int64_t* h_start_sample, int64_t* h_end_sample, double* h_start_sec, double* h_end_sec,
+                      int cap, int* n);
+/* the tap bank of torchaudio.transforms.Resample(orig, new).kernel, functional.py:1341-1400.
+ * h_taps may be NULL to query sizes; layout [phases][taps]. */
+int afe_resample_taps(int orig_hz, int new_hz, float* h_taps, size_t cap_floats,
+                      int* width, int* in_stride, int* phases, int* taps_per_phase);
+
+/* ---- device kernels ----------------------------------------------------------------- */
+/* torchaudio.transforms.Resample.forward on a [rows, length] float32 tensor
+ * (AudioProcessor.get_resampler, services/audio_processor.py:99-102).  If d_mixed is not
+ * NULL and rows == 2 it also writes mean(dim=0) = (row0 + row1)/2 (split_audio :123-131). */
+int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_t length,
+                 int orig_hz, int new_hz, float* d_out, float* d_mixed, int64_t out_length);
+
+/* mixed = (row0 + row1) * 0.5 for waveforms that need no resampling (split_audio :123-131) */
+int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed);
+
+/* processor(list_of_waveforms, sampling_rate=16000, return_tensors="pt", padding=True):
+ * SeamlessM4TFeatureExtractor.__call__ (services/audio_processor.py:253-261,
+ * services/speech_segment.py:226-231).  h_waves[b] is a DEVICE pointer to waveform b
+ * (h_lengths[b] float32 samples).
+ *
+ * group_size > 0 featurises several processor() calls in one launch: consecutive groups of
+ * group_size waveforms (the reference's batches of `batch_size` chunks,
+ * audio_processor.py:176-181) are each padded to their OWN longest member.  group_size <= 0
+ * means one group.  Group g occupies rows_g = n_g * Tp_g consecutive frame rows; d_features
+ * is (total_rows/2, 160) float32 and d_mask (total_rows/2) int32, i.e. the groups'
+ * (n_g, Tp_g/2, 160) and (n_g, Tp_g/2) tensors laid end to end.  afe_fbank_layout reports
+ * Tp_g per group (h_group_padded_frames may be NULL) and total_rows. */
+int afe_fbank_layout(const int64_t* h_lengths, int batch, int group_size,
+                     int64_t* h_group_padded_frames, int64_t* total_rows);
+size_t afe_fbank_workspace_bytes(const int64_t* h_lengths, int batch);
+int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                    int batch, int group_size, float padding_value, int precision, int flags,
+                    float* d_features, int32_t* d_mask, void* d_workspace, size_t workspace_bytes);
+
+/* AcousticSentimentAnalyzer._extract_acoustic_features for a batch of mono 16 kHz
+ * waveforms (services/sentiment_analysis.py:807-894).  d_out is (batch, 38) float32 in
+ * the reference's key order, with slot 11 ("tempo") holding the spectral-flux energy
+ * flag (> 0 -> tempo = 60 / ((F-2) * hop / sr), else 0; the host finishes it in float64);
+ * d_status[b] = 0 ok, 1 = "Audio too short" (reference returns None). */
+size_t afe_acoustic_workspace_bytes(const int64_t* h_lengths, int batch);
+int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                       int batch, int sample_rate, float* d_out, int32_t* d_status,
+                       void* d_workspace, size_t workspace_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AFE_H_ */

@@ -1,0 +1,87 @@
+"""TEST ONLY: drive the C ABI of the host-emulated kernels with numpy buffers.
+
+The emulation library (tests/_emu/libafe_emu.so) is the SAME kernel source compiled as
+plain C++; "device pointers" are numpy buffers.  It checks kernel index arithmetic in the
+GPU-less container; the product package never loads it."""
+import ctypes as C
+import functools
+
+import numpy as np
+
+from audio_processor_b200 import _native
+from audio_processor_b200.csrc import build
+
+
+@functools.lru_cache(maxsize=1)
+def emu():
+    lib = _native.Library(build.build_emu())
+    assert lib.backend == 2
+    return lib, lib.create(0)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def resample(x, orig, new, want_mixed=False):
+    lib, ctx = emu()
+    x = np.ascontiguousarray(x, np.float32)
+    rows, L = x.shape
+    Lo = lib.afe_resampled_length(L, orig, new)
+    out = np.zeros((rows, Lo), np.float32)
+    mixed = np.zeros((1, Lo), np.float32) if want_mixed else None
+    lib.check(lib.afe_resample(ctx, None, _p(x), rows, L, orig, new, _p(out), _p(mixed) if want_mixed else None, Lo))
+    return (out, mixed) if want_mixed else out
+
+
+def fbank_grouped(waves, group_size, padding_value=0.0, precision=0):
+    """Returns a list of (features, mask) per group."""
+    lib, ctx = emu()
+    waves = [np.ascontiguousarray(w, np.float32).reshape(-1) for w in waves]
+    B = len(waves)
+    lens = _native.i64_array([w.size for w in waves])
+    ptrs = _native.ptr_array([w.ctypes.data for w in waves])
+    ng = (B + group_size - 1) // group_size
+    tps = (C.c_int64 * ng)()
+    rows = C.c_int64()
+    lib.check(lib.afe_fbank_layout(lens, B, group_size, tps, C.byref(rows)))
+    ws = np.zeros(lib.afe_fbank_workspace_bytes(lens, B), np.uint8)
+    feat = np.full((rows.value // 2, 160), np.float32(-777.0), np.float32)
+    mask = np.full((rows.value // 2,), -7, np.int32)
+    lib.check(lib.afe_fbank_batch(ctx, None, ptrs, lens, B, group_size, padding_value, precision, 0,
+                                  _p(feat), _p(mask), _p(ws), ws.size))
+    out, r = [], 0
+    for g in range(ng):
+        n = min(group_size, B - g * group_size)
+        h = tps[g] // 2
+        out.append((feat[r:r + n * h].reshape(n, h, 160), mask[r:r + n * h].reshape(n, h)))
+        r += n * h
+    return out
+
+
+def fbank(waves, padding_value=0.0, precision=0, raw=False):
+    lib, ctx = emu()
+    waves = [np.ascontiguousarray(w, np.float32).reshape(-1) for w in waves]
+    B = len(waves)
+    lens = _native.i64_array([w.size for w in waves])
+    ptrs = _native.ptr_array([w.ctypes.data for w in waves])
+    Tp = lib.afe_fbank_padded_frames(lens, B)
+    ws = np.zeros(lib.afe_fbank_workspace_bytes(lens, B), np.uint8)
+    feat = np.full((B, Tp // 2, 160), np.float32(-777.0), np.float32)
+    mask = np.full((B, Tp // 2), -7, np.int32)
+    lib.check(lib.afe_fbank_batch(ctx, None, ptrs, lens, B, 0, padding_value, precision, 1 if raw else 0,
+                                  _p(feat), _p(mask), _p(ws), ws.size))
+    return feat, mask
+
+
+def acoustic(waves, sample_rate=16000):
+    lib, ctx = emu()
+    waves = [np.ascontiguousarray(w, np.float32).reshape(-1) for w in waves]
+    B = len(waves)
+    lens = _native.i64_array([w.size for w in waves])
+    ptrs = _native.ptr_array([w.ctypes.data for w in waves])
+    ws = np.zeros(lib.afe_acoustic_workspace_bytes(lens, B), np.uint8)
+    out = np.zeros((B, 38), np.float32)
+    status = np.full((B,), -1, np.int32)
+    lib.check(lib.afe_acoustic_batch(ctx, None, ptrs, lens, B, sample_rate, _p(out), _p(status), _p(ws), ws.size))
+    return out, status

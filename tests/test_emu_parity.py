@@ -1,0 +1,111 @@
+"""Kernel logic vs oracle / golden, run through the C ABI of the host emulation (CPU)."""
+import numpy as np
+import pytest
+
+from oracle import np_fbank, np_resample
+from tests import emu_util
+
+
+def _split(flat, lengths):
+    out, o = [], 0
+    for n in lengths:
+        out.append(flat[o:o + int(n)]); o += int(n)
+    return out
+
+
+def _cmp_nan(a, b, tol):
+    assert a.shape == b.shape
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = ~np.isnan(b)
+    return float(np.max(np.abs(a[ok] - b[ok]), initial=0.0)) <= tol
+
+
+# ------------------------------------------------------------------ resample: bit-exact
+@pytest.mark.parametrize("src,pre", [("x8", ""), ("xw8", "w_")])
+def test_emu_resample_split_bit_exact(golden, src, pre):
+    g = golden("resample")
+    out, mixed = emu_util.resample(g[src], 8000, 16000, want_mixed=True)
+    assert np.array_equal(out[0:1], g[pre + "agent16"])
+    assert np.array_equal(out[1:2], g[pre + "client16"])
+    assert np.array_equal(mixed, g[pre + "mixed16"])
+
+
+def test_emu_resample_mono_and_44k(golden):
+    g = golden("resample")
+    assert np.array_equal(emu_util.resample(g["xm8"], 8000, 16000), g["m_agent16"])
+    assert np.array_equal(emu_util.resample(g["x44_long"], 44100, 16000), g["y44to16_long"])
+    assert np.max(np.abs(emu_util.resample(g["x44"], 44100, 16000) - g["y44to16"])) <= 1.2e-7
+
+
+@pytest.mark.parametrize("L", [1, 3, 7, 1023, 1024, 1025, 2049])
+def test_emu_resample_ragged_lengths(L):
+    x = (np.random.default_rng(L).uniform(-0.5, 0.5, (2, L))).astype(np.float32)
+    out, mixed = emu_util.resample(x, 8000, 16000, want_mixed=True)
+    ref = np_resample.resample(x, 8000, 16000)
+    assert np.array_equal(out, ref)
+    assert np.array_equal(mixed[0], (ref[0] + ref[1]) * np.float32(0.5))
+
+
+def test_emu_resample_generic_rates():
+    x = (np.random.default_rng(5).uniform(-0.5, 0.5, (1, 3000))).astype(np.float32)
+    for orig, new in ((16000, 8000), (48000, 16000), (22050, 16000)):
+        assert np.array_equal(emu_util.resample(x, orig, new), np_resample.resample(x, orig, new)), (orig, new)
+
+
+# ------------------------------------------------------------------ fbank
+def test_emu_fbank_ragged_batch(golden):
+    g = golden("fbank")
+    waves = _split(g["ragged_waves"], g["ragged_lengths"])
+    feat, mask = emu_util.fbank(waves)
+    assert np.array_equal(mask, g["ragged_mask"])
+    assert _cmp_nan(feat, g["ragged_features"], 1e-3)
+
+
+@pytest.mark.parametrize("n", [399, 400, 559, 560, 720])
+def test_emu_fbank_degenerate(golden, n):
+    g = golden("fbank")
+    feat, mask = emu_util.fbank([g[f"single_{n}_wave"]])
+    assert np.array_equal(mask, g[f"single_{n}_mask"])
+    assert _cmp_nan(feat, g[f"single_{n}_features"], 1e-3)
+
+
+@pytest.mark.parametrize("name", ["up8k", "white", "tone1k", "zeros"])
+def test_emu_fbank_signals(golden, name):
+    g = golden("fbank")
+    w = g[f"{name}_wave"]
+    raw, _ = emu_util.fbank([w], raw=True)
+    T = np_fbank.num_frames(w.size)
+    raw = raw.reshape(1, -1, 80)[0, :T]
+    assert np.max(np.abs(raw - g[f"{name}_raw"])) <= (2e-4 if name == "tone1k" else 2e-5), name
+    if name in ("up8k", "white"):
+        feat, mask = emu_util.fbank([w])
+        assert np.array_equal(mask, g[f"{name}_mask"])
+        assert _cmp_nan(feat, g[f"{name}_features"], 1e-3 if name == "up8k" else 2e-4)
+
+
+def test_emu_fbank_padding_value_and_f32(golden):
+    g = golden("fbank")
+    waves = _split(g["ragged_waves"], g["ragged_lengths"])
+    feat, mask = emu_util.fbank(waves, padding_value=1.0)
+    ref = g["ragged_features"].reshape(len(waves), -1, 80)
+    got = feat.reshape(len(waves), -1, 80)
+    for b, n in enumerate(g["ragged_lengths"]):
+        T = np_fbank.num_frames(int(n))
+        assert np.all(got[b, T:] == 1.0)
+        assert _cmp_nan(got[b, :T], ref[b, :T], 1e-3)
+    feat32, mask32 = emu_util.fbank(waves, precision=1)
+    assert np.array_equal(mask32, mask)
+    assert _cmp_nan(feat32, g["ragged_features"], 2e-2)      # opt-in fast path: looser by design
+
+
+def test_emu_fbank_grouped_matches_per_group_calls(golden):
+    g = golden("fbank")
+    waves = _split(g["ragged_waves"], g["ragged_lengths"])
+    order = [6, 0, 5, 3, 1, 2, 4]
+    waves = [waves[i] for i in order]
+    groups = emu_util.fbank_grouped(waves, 3)
+    assert len(groups) == 3
+    for gi, (feat, mask) in enumerate(groups):
+        ref_f, ref_m = np_fbank.featurise(waves[3 * gi:3 * gi + 3])
+        assert np.array_equal(mask, ref_m)
+        assert _cmp_nan(feat, ref_f, 1e-3)
