@@ -1,0 +1,142 @@
+"""Drop-in for the hot-path methods of the reference's ``AudioProcessor``
+(services/audio_processor.py): ``get_resampler`` (:99-102), ``split_audio`` (:104-160),
+the length bucketing of ``transcribe_batch`` (:170-181) and the featurise step of
+``_run_inference`` (:253-266).  Model loading, decoding and the database are out of scope
+ and stay with the reference.
+
+Output placement: waveforms and chunk views live on the CUDA device (they feed the fbank
+and acoustic kernels directly, without the reference's ``.numpy()`` hop).  Everything
+integer -- chunk boundaries, ``start_time`` / ``end_time`` floats, ``chunk_idx`` -- is
+bit-identical to the reference.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from functools import lru_cache
+from typing import Any, Dict, List, Sequence, Tuple
+
+import torch
+
+from . import _native, runtime
+from .feature_extractor import FbankFeatureExtractor, FbankProcessor
+
+
+def chunk_table(total_samples: int, chunk_samples: int, step_samples: int) -> List[Tuple[int, int]]:
+    """(start, end) sample pairs of ``split_audio``'s while-loop, from the C ABI."""
+    lib = _native.load()
+    n = C.c_int(0)
+    lib.check(lib.afe_chunk_table(int(total_samples), int(chunk_samples), int(step_samples), None, None, 0, C.byref(n)))
+    starts = (C.c_int64 * max(1, n.value))()
+    ends = (C.c_int64 * max(1, n.value))()
+    lib.check(lib.afe_chunk_table(int(total_samples), int(chunk_samples), int(step_samples), starts, ends, n.value,
+                                  C.byref(n)))
+    return [(int(starts[i]), int(ends[i])) for i in range(n.value)]
+
+
+class Resampler:
+    """Callable with the behaviour of ``torchaudio.transforms.Resample(orig, new)``."""
+
+    def __init__(self, orig_freq: int, new_freq: int, device=None):
+        self.orig_freq, self.new_freq = int(orig_freq), int(new_freq)
+        self._device = device
+
+    def __call__(self, waveform: torch.Tensor) -> torch.Tensor:
+        if self.orig_freq == self.new_freq:
+            return waveform
+        fe = runtime.get_frontend(self._device)
+        return fe.resample(waveform.to(fe.device, non_blocking=True), self.orig_freq, self.new_freq)
+
+    forward = __call__
+
+
+class AudioProcessor:
+    """``AudioProcessor(config)`` with the reference's config keys
+    (``chunk_duration_sec``, ``overlap_sec``, ``target_sample_rate``, ``batch_size`` /
+    ``chunk_batch_size``, ``enable_length_bucketing``, ``gpu_index``)."""
+
+    def __init__(self, config: dict, db_manager=None, processor=None):
+        self.config = config
+        gpu_index = int(config.get("gpu_index", 0))
+        self.device = torch.device(f"cuda:{gpu_index}")
+        self.frontend = runtime.get_frontend(self.device)
+        self.db_manager = db_manager
+        self.chunk_duration_sec = config["chunk_duration_sec"]
+        self.overlap_sec = config.get("overlap_sec", 1)
+        self.target_sample_rate = config.get("target_sample_rate", 16000)
+        self.processor = processor or FbankProcessor(FbankFeatureExtractor(device=self.device))
+        self.model = None
+
+    # -------------------------------------------------------------- reference :99-102
+    @lru_cache(maxsize=100)
+    def get_resampler(self, orig_freq: int, new_freq: int) -> Resampler:
+        return Resampler(orig_freq, new_freq, self.device)
+
+    # -------------------------------------------------------------- reference :104-160
+    def split_audio(self, waveform: torch.Tensor, sample_rate: int, file_name: str):
+        fe = self.frontend
+        waveform = waveform.to(fe.device, non_blocking=True)
+        mixed = None
+        if sample_rate != self.target_sample_rate:
+            if waveform.shape[0] == 2:
+                waveform, mixed = fe.resample(waveform, sample_rate, self.target_sample_rate, want_mixed=True)
+            else:
+                waveform = fe.resample(waveform, sample_rate, self.target_sample_rate)
+            sample_rate = self.target_sample_rate
+        chunk_samples = int(self.chunk_duration_sec * sample_rate)
+        overlap_samples = int(self.overlap_sec * sample_rate)
+        step_samples = chunk_samples - overlap_samples
+        total_samples = waveform.shape[1]
+        if waveform.shape[0] == 2:
+            agent_waveform = waveform[0].unsqueeze(0)
+            client_waveform = waveform[1].unsqueeze(0)
+            mixed_waveform = mixed if mixed is not None else fe.mix_stereo(waveform)
+        else:
+            agent_waveform = client_waveform = mixed_waveform = waveform
+        chunks: List[Dict[str, Any]] = []
+        for chunk_idx, (start, end) in enumerate(chunk_table(total_samples, chunk_samples, step_samples)):
+            chunks.append({
+                "file_name": f"{file_name}",
+                "stereo_waveform": mixed_waveform[:, start:end],
+                "agent_waveform": agent_waveform[:, start:end],
+                "client_waveform": client_waveform[:, start:end],
+                "chunk_idx": chunk_idx,
+                "start_time": start / sample_rate,
+                "end_time": end / sample_rate,
+            })
+        return chunks, agent_waveform, client_waveform
+
+    # -------------------------------------------------------------- reference :170-181
+    def bucket_chunks(self, chunks: Sequence[Dict]) -> List[List[Dict]]:
+        """The stable length sort and ``batch_size`` slicing of ``transcribe_batch``."""
+        batch_size = int(self.config.get("batch_size", self.config.get("chunk_batch_size", 16)))
+        chunks = list(chunks)
+        if bool(self.config.get("enable_length_bucketing", True)):
+            chunks = sorted(chunks, key=lambda c: int(c.get("stereo_waveform", c.get("agent_waveform")).shape[1]))
+        return [chunks[i:i + batch_size] for i in range(0, len(chunks), batch_size)]
+
+    # -------------------------------------------------------------- reference :253-266
+    def featurise_batch(self, batch_chunks: Sequence[Dict]) -> Dict[str, torch.Tensor]:
+        """The three ``processor(...)`` calls of ``_run_inference`` for one batch of chunks:
+        ``{"stereo"|"agent"|"client": input_features (B, T/2, 160)}`` (+ ``*_mask``)."""
+        out: Dict[str, torch.Tensor] = {}
+        for key, field in (("stereo", "stereo_waveform"), ("agent", "agent_waveform"), ("client", "client_waveform")):
+            arrays = [c[field].squeeze(0) for c in batch_chunks]
+            inputs = self.processor(arrays, sampling_rate=16000, return_tensors="pt", padding=True)
+            out[key] = inputs["input_features"]
+            out[key + "_mask"] = inputs["attention_mask"]
+        return out
+
+    def featurise_all(self, chunks: Sequence[Dict]):
+        """All batches of ``transcribe_batch`` in three launches (one per stream): a list of
+        ``(batch_chunks, {"stereo": (feat, mask), "agent": .., "client": ..})``."""
+        batches = self.bucket_chunks(chunks)
+        if not batches:
+            return []
+        flat = [c for b in batches for c in b]
+        gs = int(self.config.get("batch_size", self.config.get("chunk_batch_size", 16)))
+        fx = self.processor.feature_extractor
+        per_stream = {}
+        for key, field in (("stereo", "stereo_waveform"), ("agent", "agent_waveform"), ("client", "client_waveform")):
+            per_stream[key] = self.frontend.fbank([c[field].squeeze(0) for c in flat], padding_value=fx.padding_value,
+                                                  precision=fx.precision, group_size=gs)
+        return [(b, {k: per_stream[k][i] for k in per_stream}) for i, b in enumerate(batches)]

@@ -109,3 +109,31 @@ def test_emu_fbank_grouped_matches_per_group_calls(golden):
         ref_f, ref_m = np_fbank.featurise(waves[3 * gi:3 * gi + 3])
         assert np.array_equal(mask, ref_m)
         assert _cmp_nan(feat, ref_f, 1e-3)
+
+
+# ------------------------------------------------------------------ acoustic
+def _tempo_from_flag(flag, L):
+    F2 = 1 + L // 160
+    lag = (F2 - 2) if flag > 0 else 0
+    period = lag * 160 / 16000 if lag > 0 else 0.0
+    return 60.0 / period if period > 0 else 0.0
+
+
+def test_emu_acoustic_golden(golden):
+    g = golden("acoustic")
+    names = [str(n) for n in g["names"]]
+    waves = [g[f"{n}_wave"] for n in names] + [np.zeros(399, np.float32)]
+    out, status = emu_util.acoustic(waves)
+    assert status.tolist() == [0] * len(names) + [1]
+    assert np.all(out[-1] == 0)
+    for i, name in enumerate(names):
+        ref = g[f"{name}_values"]
+        got = out[i].astype(np.float64)
+        got[11] = _tempo_from_flag(out[i, 11], waves[i].size)
+        assert got[11] == ref[11], name                                     # tempo exact
+        assert np.array_equal(np.isnan(got), np.isnan(ref)), name
+        ok = ~np.isnan(ref)
+        rel = 5e-3 if name.split("_")[0] in ("tone", "dc", "square") else 1e-4
+        tol = np.maximum(1e-3, rel * np.abs(ref))
+        bad = [(k, got[k], ref[k]) for k in range(38) if ok[k] and abs(got[k] - ref[k]) > tol[k]]
+        assert not bad, (name, bad)

@@ -1,0 +1,245 @@
+"""Parity of the CUDA path (through the C ABI / runtime) against golden vectors and the
+oracle.  Needs a B200; run with ``pytest -m gpu``."""
+import numpy as np
+import pytest
+
+from oracle import np_fbank, np_resample, np_tables
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fe():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from audio_processor_b200 import runtime
+    return runtime.get_frontend(0)
+
+
+def _t(a, fe):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(fe.device)
+
+
+def _split(flat, lengths):
+    out, o = [], 0
+    for n in lengths:
+        out.append(flat[o:o + int(n)]); o += int(n)
+    return out
+
+
+def _cmp_nan(a, b, tol):
+    assert a.shape == b.shape
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = ~np.isnan(b)
+    err = float(np.max(np.abs(a[ok] - b[ok]), initial=0.0))
+    assert err <= tol, err
+
+
+def test_native_library_is_cuda_build(fe):
+    assert fe.lib.backend == 1 and fe.num_sms >= 100
+
+
+# ------------------------------------------------------------------ resample (bit-exact)
+@pytest.mark.parametrize("src,pre", [("x8", ""), ("xw8", "w_")])
+def test_resample_split_bit_exact(fe, golden, src, pre):
+    g = golden("resample")
+    out, mixed = fe.resample(_t(g[src], fe), 8000, 16000, want_mixed=True)
+    out, mixed = out.cpu().numpy(), mixed.cpu().numpy()
+    assert np.array_equal(out[0:1], g[pre + "agent16"])
+    assert np.array_equal(out[1:2], g[pre + "client16"])
+    assert np.array_equal(mixed, g[pre + "mixed16"])
+
+
+def test_resample_mono_44k_generic(fe, golden):
+    g = golden("resample")
+    assert np.array_equal(fe.resample(_t(g["xm8"], fe), 8000, 16000).cpu().numpy(), g["m_agent16"])
+    assert np.array_equal(fe.resample(_t(g["x44_long"], fe), 44100, 16000).cpu().numpy(), g["y44to16_long"])
+    x = (np.random.default_rng(5).uniform(-0.5, 0.5, (1, 3000))).astype(np.float32)
+    for orig, new in ((16000, 8000), (48000, 16000), (22050, 16000)):
+        assert np.array_equal(fe.resample(_t(x, fe), orig, new).cpu().numpy(), np_resample.resample(x, orig, new))
+
+
+@pytest.mark.parametrize("L", [1, 3, 7, 1023, 1024, 1025, 2049, 100001])
+def test_resample_ragged_lengths(fe, L):
+    x = (np.random.default_rng(L).uniform(-0.5, 0.5, (2, L))).astype(np.float32)
+    out, mixed = fe.resample(_t(x, fe), 8000, 16000, want_mixed=True)
+    ref = np_resample.resample(x, 8000, 16000)
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert np.array_equal(mixed.cpu().numpy()[0], (ref[0] + ref[1]) * np.float32(0.5))
+
+
+# ------------------------------------------------------------------ fbank
+def test_fbank_ragged_batch(fe, golden):
+    g = golden("fbank")
+    waves = _split(g["ragged_waves"], g["ragged_lengths"])
+    feat, mask = fe.fbank(waves)
+    assert np.array_equal(mask.cpu().numpy(), g["ragged_mask"])
+    _cmp_nan(feat.cpu().numpy(), g["ragged_features"], 1e-3)      # tolerance of the north star
+
+
+@pytest.mark.parametrize("n", [399, 400, 559, 560, 720])
+def test_fbank_degenerate(fe, golden, n):
+    g = golden("fbank")
+    feat, mask = fe.fbank([g[f"single_{n}_wave"]])
+    assert np.array_equal(mask.cpu().numpy(), g[f"single_{n}_mask"])
+    _cmp_nan(feat.cpu().numpy(), g[f"single_{n}_features"], 1e-3)
+
+
+@pytest.mark.parametrize("name", ["up8k", "white"])
+def test_fbank_signals(fe, golden, name):
+    g = golden("fbank")
+    w = g[f"{name}_wave"]
+    feat, mask = fe.fbank([w])
+    assert np.array_equal(mask.cpu().numpy(), g[f"{name}_mask"])
+    _cmp_nan(feat.cpu().numpy(), g[f"{name}_features"], 1e-3)
+    raw, _ = fe.fbank([w], raw=True)
+    T = np_fbank.num_frames(w.size)
+    assert np.max(np.abs(raw.cpu().numpy().reshape(1, -1, 80)[0, :T] - g[f"{name}_raw"])) <= 5e-5
+
+
+def test_fbank_grouped_and_device_inputs(fe, golden):
+    g = golden("fbank")
+    waves = _split(g["ragged_waves"], g["ragged_lengths"])
+    order = [6, 0, 5, 3, 1, 2, 4]
+    waves = [waves[i] for i in order]
+    groups = fe.fbank([_t(w, fe) for w in waves], group_size=3, padding_value=1.0)
+    assert len(groups) == 3
+    for gi, (feat, mask) in enumerate(groups):
+        ref_f, ref_m = np_fbank.featurise(waves[3 * gi:3 * gi + 3], padding_value=1.0)
+        assert np.array_equal(mask.cpu().numpy(), ref_m)
+        _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+
+
+def test_fbank_f32_fast_path_is_looser(fe, golden):
+    g = golden("fbank")
+    from audio_processor_b200 import _native
+    feat, mask = fe.fbank([g["up8k_wave"]], precision=_native.PRECISION_F32)
+    assert np.array_equal(mask.cpu().numpy(), g["up8k_mask"])
+    _cmp_nan(feat.cpu().numpy(), g["up8k_features"], 2e-2)
+
+
+def test_chain_cfg1_resample_chunk_fbank(fe):
+    """cfg1: 60 s stereo 8 kHz call -> resample/split -> 25 s chunks -> fbank of each stream."""
+    from audio_processor_b200 import synth
+    call, sr = synth.cfg1_call()
+    out, mixed = fe.resample(call.to(fe.device), sr, 16000, want_mixed=True)
+    ref = np_resample.resample(call.numpy(), sr, 16000)
+    assert np.array_equal(out.cpu().numpy(), ref)                 # bit-exact resample
+    table = np_tables.chunk_table(out.shape[1], 16000, 25, 1)
+    assert [(s, e) for s, e, _, _ in table] == [(0, 400000), (384000, 784000), (768000, 960000)]
+    agent = out[0]
+    chunks = [agent[s:e] for s, e, _, _ in table]
+    feat, mask = fe.fbank(chunks)
+    ref_f, ref_m = np_fbank.featurise([ref[0, s:e] for s, e, _, _ in table])
+    assert tuple(feat.shape) == (3, 1249, 160) and mask.sum(1).tolist() == [1249, 1249, 599]
+    assert np.array_equal(mask.cpu().numpy(), ref_m)
+    _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+
+
+# ------------------------------------------------------------------ acoustic
+def test_acoustic_golden(fe, golden):
+    from audio_processor_b200 import acoustic
+    g = golden("acoustic")
+    names = [str(n) for n in g["names"]]
+    waves = [g[f"{n}_wave"] for n in names] + [np.zeros(399, np.float32)]
+    feats = acoustic.extract_acoustic_features_batch(waves, 16000, fe.device)
+    assert feats[-1] is None
+    for name, f in zip(names, feats):
+        ref = g[f"{name}_values"]
+        assert list(f.keys()) == [str(k) for k in g[f"{name}_keys"]]
+        got = np.asarray(list(f.values()), np.float64)
+        assert got[11] == ref[11], name
+        assert np.array_equal(np.isnan(got), np.isnan(ref)), name
+        ok = ~np.isnan(ref)
+        rel = 5e-3 if name.split("_")[0] in ("tone", "dc", "square") else 1e-4
+        tol = np.maximum(1e-3, rel * np.abs(ref))
+        bad = [(k, got[k], ref[k]) for k in range(38) if ok[k] and abs(got[k] - ref[k]) > tol[k]]
+        assert not bad, (name, bad)
+
+
+def test_acoustic_drop_in_object(fe, golden):
+    import torch
+    from audio_processor_b200 import acoustic
+    g = golden("acoustic")
+    ex = acoustic.AcousticFeatureExtractor(fe.device)
+    f = ex._extract_acoustic_features(torch.from_numpy(g["white_32000_wave"])[None, :], 16000)
+    assert len(f) == 38 and abs(f["mfcc_0_mean"] - g["white_32000_values"][12]) <= 1e-3
+    assert ex._extract_acoustic_features(torch.zeros(1, 399), 16000) is None
+    assert list(ex._get_zero_features().keys()) == acoustic.FEATURE_KEYS
+
+
+# ------------------------------------------------------------------ drop-in classes
+def test_audio_processor_drop_in(fe):
+    import torch
+    from audio_processor_b200 import AudioProcessor, synth
+    cfg = {"chunk_duration_sec": 25, "overlap_sec": 1, "target_sample_rate": 16000, "batch_size": 16, "gpu_index": 0}
+    ap = AudioProcessor(cfg)
+    call, sr = synth.cfg1_call()
+    chunks, agent, client = ap.split_audio(call, sr, "f.wav")
+    assert [c["chunk_idx"] for c in chunks] == [0, 1, 2]
+    assert [(c["start_time"], c["end_time"]) for c in chunks] == [(0.0, 25.0), (24.0, 49.0), (48.0, 60.0)]
+    assert list(chunks[0].keys()) == ["file_name", "stereo_waveform", "agent_waveform", "client_waveform",
+                                      "chunk_idx", "start_time", "end_time"]
+    ref = np_resample.resample(call.numpy(), sr, 16000)
+    assert np.array_equal(agent.cpu().numpy(), ref[0:1]) and np.array_equal(client.cpu().numpy(), ref[1:2])
+    assert np.array_equal(chunks[2]["stereo_waveform"].cpu().numpy()[0], ((ref[0] + ref[1]) * np.float32(0.5))[768000:])
+    # the processor() call of _run_inference on the length-sorted batch
+    batches = ap.bucket_chunks(chunks)
+    assert [c["chunk_idx"] for c in batches[0]] == [2, 0, 1]
+    out = ap.featurise_batch(batches[0])
+    ref_f, ref_m = np_fbank.featurise([ref[1, 768000:], ref[1, :400000], ref[1, 384000:784000]])
+    assert np.array_equal(out["client_mask"].cpu().numpy(), ref_m)
+    _cmp_nan(out["client"].cpu().numpy(), ref_f, 1e-3)
+    allb = ap.featurise_all(chunks)
+    assert torch.equal(allb[0][1]["client"][0], out["client"])
+    # resampler object and the ValueError of a wrong sampling rate
+    assert ap.get_resampler(8000, 16000) is ap.get_resampler(8000, 16000)
+    with pytest.raises(ValueError):
+        ap.processor([np.zeros(1000, np.float32)], sampling_rate=8000, return_tensors="pt", padding=True)
+
+
+def test_speech_segment_drop_in(fe, golden):
+    import torch
+    from audio_processor_b200 import SpeechSegment
+    g = golden("tables")
+    cfg = {"gpu_index": 0, "batch_size": 4, "vad_max_segment_sec": 25.0, "vad_window_overlap_sec": 0.5,
+           "vad_gap_threshold": 0.8, "vad_padding": 0.5}
+    n = int(g["seg_num_samples"][0])
+    wf = (torch.rand(1, n, generator=torch.Generator().manual_seed(3)) - 0.5).to(fe.device)
+    seg = SpeechSegment(cfg)
+    ex = seg._extract_segments(wf, 16000, [tuple(r) for r in g["seg_intervals"]], "agent", 0.5)
+    exp = g["seg_cfg"]
+    assert len(ex) == len(exp)
+    for e, r in zip(ex, exp):
+        assert e["segment_waveform"].shape[1] == int(r[0]) and e["start"] == r[1] and e["end"] == r[2]
+        assert e["speaker"] == "agent"
+    assert np.array_equal(np.asarray(seg._merge_segments([tuple(r) for r in g["merge_in"]], 0.8)), g["merge_out"])
+    groups = seg.featurise_segments(ex[:5], 16000)
+    lens = sorted((e["segment_waveform"].shape[1], i) for i, e in enumerate(ex[:5]))
+    assert [i for idxs, _, _ in groups for i in idxs] == [i for _, i in lens]
+    idxs, feat, mask = groups[0]
+    ref_f, ref_m = np_fbank.featurise([ex[i]["segment_waveform"][0].cpu().numpy() for i in idxs])
+    assert np.array_equal(mask.cpu().numpy(), ref_m)
+    _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+
+
+def test_call_frontend_whole_path(fe):
+    from audio_processor_b200 import CallFrontend, synth
+    from oracle import np_acoustic
+    calls = [synth.make_call(30.0, 8000, 77, 2), synth.make_call(12.5, 8000, 78, 2)]
+    cf = CallFrontend(fe.device, batch_size=2)
+    res = cf.process_calls(calls, 8000)
+    assert [(c, i) for c, i, _, _ in res.chunks] == [(0, 0), (0, 1), (1, 0)]
+    assert res.order == [1, 2, 0] and len(res.features["agent"]) == 2
+    ref0 = np_resample.resample(calls[0].numpy(), 8000, 16000)
+    ref1 = np_resample.resample(calls[1].numpy(), 8000, 16000)
+    ref_f, ref_m = np_fbank.featurise([ref0[0, 384000:], ref1[0]])
+    feat, mask = res.features["agent"][0]
+    assert np.array_equal(mask.cpu().numpy(), ref_m)
+    _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+    agent_d, client_d = cf.acoustic_dicts(res)
+    ref_a = np_acoustic.acoustic_features(ref1[1])
+    got = np.asarray(list(client_d[2].values())); exp = np.asarray(list(ref_a.values()))
+    assert np.all(np.abs(got - exp) <= np.maximum(2e-3, 2e-4 * np.abs(exp)))

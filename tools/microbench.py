@@ -1,0 +1,65 @@
+"""Kernel-level timing of the front end stages with CUDA events (development aid).
+
+    python tools/microbench.py [--chunks 96] [--reps 10]
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from audio_processor_b200 import _native, runtime  # noqa: E402
+
+
+def timed(fn, reps, flush):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(reps):
+        flush.zero_()                      # evict L2 (buffer > 126 MB)
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    ms.sort()
+    return ms[len(ms) // 2], ms[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--chunks", type=int, default=96)
+    ap.add_argument("--reps", type=int, default=10)
+    ap.add_argument("--only", default="")
+    a = ap.parse_args()
+    fe = runtime.get_frontend(0)
+    dev = fe.device
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    g = torch.Generator(device="cpu"); g.manual_seed(0)
+    res = {"num_sms": fe.num_sms}
+    # resample: one 5-min stereo 8 kHz call
+    if not a.only or a.only == "resample":
+        call = (torch.rand(2, 2_400_000, generator=g) - 0.5).to(dev)
+        med, best = timed(lambda: fe.resample(call, 8000, 16000, want_mixed=True), a.reps, flush)
+        byts = 2_400_000 * 2 * 4 + 3 * 4_800_000 * 4
+        res["resample_8k_stereo_5min"] = {"ms_med": med, "ms_best": best, "GBps_best": byts / best / 1e6}
+    # fbank on N full 25 s chunks
+    wav = (torch.rand(a.chunks, 400_000, generator=g) - 0.5).to(dev)
+    chunks = [wav[i] for i in range(a.chunks)]
+    frames = a.chunks * 2498
+    for name, prec in (("fbank_f64", _native.PRECISION_F64), ("fbank_f32", _native.PRECISION_F32)):
+        if a.only and a.only != name:
+            continue
+        med, best = timed(lambda: fe.fbank(chunks, precision=prec, group_size=16), a.reps, flush)
+        res[name] = {"ms_med": med, "ms_best": best, "Mframes_per_s": frames / best / 1e3,
+                     "algorithmic_GBps": frames * 962 / best / 1e6}
+        med, best = timed(lambda: fe.fbank(chunks, precision=prec, group_size=16, raw=True), a.reps, flush)
+        res[name + "_rawonly"] = {"ms_med": med, "ms_best": best, "Mframes_per_s": frames / best / 1e3,
+                                  "algorithmic_GBps": frames * 962 / best / 1e6}
+    print(json.dumps(res, indent=1))
+
+
+if __name__ == "__main__":
+    main()
