@@ -23,6 +23,7 @@ AFE_ERR_UNSUPPORTED = -4
 PRECISION_F64 = 0
 PRECISION_F32 = 1
 FBANK_RAW = 1
+K_COUNT = 9
 
 c_i64p = C.POINTER(C.c_int64)
 c_i32p = C.POINTER(C.c_int32)
@@ -64,6 +65,10 @@ SIGNATURES = {
     "afe_fbank_workspace_bytes": (C.c_size_t, [c_i64p, C.c_int]),
     "afe_fbank_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
                                   C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "afe_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
+    "afe_profile_reset": (C.c_int, [C.c_void_p]),
+    "afe_profile_read": (C.c_int, [C.c_void_p, c_f64p, c_i64p]),
+    "afe_kernel_name": (C.c_char_p, [C.c_int]),
     "afe_acoustic_workspace_bytes": (C.c_size_t, [c_i64p, C.c_int]),
     "afe_acoustic_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),

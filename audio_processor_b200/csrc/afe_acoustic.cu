@@ -111,14 +111,21 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
   tk.d = d; tk.hann = ctx->d_hann32; tk.tw512 = ctx->d_tw32;
   tk.mel_start = ctx->d_htk_start; tk.mel_count = ctx->d_htk_count; tk.mel_offset = ctx->d_htk_offset;
   tk.mel_w = ctx->d_htk_w; tk.meldb = meldb; tk.tile_rec = tile_rec; tk.boundary = boundary;
-  int rc = afe_launch(tk, AcSmem::kBytes, ctx->num_sms, s);
-  if (rc == 0) { AcousticMaxKernel mk{d, tile_rec, gmax}; rc = afe_launch(mk, 0, 1 << 20, s); }
+  int rc;
+  { ProfScope ps(ctx, AFE_K_AC_TILE, s); rc = afe_launch(tk, AcSmem::kBytes, ctx->num_sms, s); }
+  if (rc == 0) {
+    AcousticMaxKernel mk{d, tile_rec, gmax};
+    ProfScope ps(ctx, AFE_K_AC_MAX, s);
+    rc = afe_launch(mk, 0, 1 << 20, s);
+  }
   if (rc == 0) {
     AcousticMfccKernel ck{d, meldb, gmax, ctx->d_dct, mfcc_rec};
+    ProfScope ps(ctx, AFE_K_AC_MFCC, s);
     rc = afe_launch(ck, AcousticMfccKernel::kSmemBytes, ctx->num_sms * 4, s);
   }
   if (rc == 0) {
     AcousticFinalKernel fk{d, tile_rec, mfcc_rec, boundary, d_out, d_status};
+    ProfScope ps(ctx, AFE_K_AC_FINAL, s);
     rc = afe_launch(fk, 0, 1 << 20, s);
   }
   if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_acoustic_batch: launch failed: ") + dev_last_error_string());

@@ -31,6 +31,8 @@ struct StagingBlock {
 
 }  // namespace afe
 
+namespace afe { struct ProfScope; }
+
 struct afe_ctx {
   int device = 0;
   int num_sms = afe::kNumSMsB200;
@@ -49,6 +51,13 @@ struct afe_ctx {
   std::map<std::pair<int, int>, afe::DeviceTaps> taps;          // (orig, new) -> bank
   std::vector<afe::StagingBlock> staging;
   std::vector<void*> owned;                                     // device allocations to free
+  // optional per-kernel timing (afe_profile_*): (kernel id, start event, stop event)
+  bool profiling = false;
+  struct ProfRec { int id; void* e0; void* e1; };
+  std::vector<ProfRec> prof_recs;
+  std::vector<void*> prof_free;                                 // recycled events
+  int64_t prof_launches[AFE_K_COUNT] = {0};
+  void* prof_event();
 
   // returns a pinned block of >= bytes (nullptr on failure); call staging_submit after the copy
   afe::StagingBlock* staging_acquire(size_t bytes);
@@ -62,3 +71,12 @@ struct afe_ctx {
     return p;
   }
 };
+
+namespace afe {
+// brackets one kernel launch with events when profiling is on; always counts the launch
+struct ProfScope {
+  afe_ctx* c; int id; cudaStream_t s; void* e1 = nullptr;
+  ProfScope(afe_ctx* ctx, int kernel_id, cudaStream_t stream);
+  ~ProfScope();
+};
+}  // namespace afe

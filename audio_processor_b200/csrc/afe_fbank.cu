@@ -46,6 +46,7 @@ int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, dou
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
   k.mel_start = ctx->d_mel_start; k.mel_count = ctx->d_mel_count; k.mel_offset = ctx->d_mel_offset;
   k.mel_w = ctx->d_mel_w; k.log_floor = ctx->log_floor;
+  ProfScope ps(ctx, AFE_K_FBANK, s);
   return afe_launch(k, FbankSmem<T>::kBytes, ctx->num_sms, s);
 }
 
@@ -136,12 +137,13 @@ int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, con
                : run_fbank<float>(ctx, s, d, d_features, partials, ctx->d_povey32, ctx->d_tw32);
   if (rc == 0 && !raw_only && rows > 0) {
     FbankStatsKernel sk{d, partials, stats};
-    rc = afe_launch(sk, 0, 1 << 20, s);
+    { ProfScope ps(ctx, AFE_K_FBANK_STATS, s); rc = afe_launch(sk, 0, 1 << 20, s); }
     if (rc == 0) {
       FbankNormKernel nk;
       nk.d = d; nk.feat = d_features; nk.mask = d_mask; nk.stats = stats;
       nk.padding_value = padding_value;
       nk.items_per_utt = (long)((tp_max * kMel + FbankNormKernel::kItemFloats - 1) / FbankNormKernel::kItemFloats);
+      ProfScope ps(ctx, AFE_K_FBANK_NORM, s);
       rc = afe_launch(nk, 0, ctx->num_sms * 8, s);
     }
   }

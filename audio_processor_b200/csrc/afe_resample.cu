@@ -27,6 +27,7 @@ extern "C" {
 int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed) {
   if (!ctx || !d_in || !d_mixed || length < 0) return fail(AFE_ERR_INVALID, "afe_mix_stereo: bad arguments");
   MixKernel k{d_in, d_mixed, length};
+  ProfScope ps(ctx, AFE_K_MIX, (cudaStream_t)stream);
   if (afe_launch(k, 0, ctx->num_sms * 8, (cudaStream_t)stream) != 0) return fail(AFE_ERR_CUDA, "afe_mix_stereo: launch failed");
   return AFE_OK;
 }
@@ -45,6 +46,8 @@ int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_
   const ResampleTaps& t = dt->host;
   cudaStream_t s = (cudaStream_t)stream;
   int rc;
+  {
+  ProfScope ps(ctx, AFE_K_RESAMPLE, s);
   if (t.O == 1 && t.N == 2 && t.K == 15) {
     const long ipr = (long)((length + 1023) / 1024);
     if (rows == 2 && d_mixed) {
@@ -68,9 +71,13 @@ int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_
     const size_t smem = k.smem_bytes();
     if (smem > 200 * 1024) return fail(AFE_ERR_UNSUPPORTED, "afe_resample: tap tile exceeds shared memory for this rate pair");
     rc = afe_launch(k, smem, ctx->num_sms * 2, s);
+  }
+  }
+  if (!(t.O == 1 && t.N == 2 && t.K == 15)) {
     if (rc == 0 && d_mixed) {
       // generic path: mix the two resampled rows afterwards
       MixKernel m{d_out, d_mixed, out_length};
+      ProfScope pm(ctx, AFE_K_MIX, s);
       rc = afe_launch(m, 0, ctx->num_sms * 8, s);
     }
   }

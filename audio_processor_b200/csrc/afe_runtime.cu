@@ -110,7 +110,78 @@ const afe::DeviceTaps* afe_ctx::get_taps(int orig_hz, int new_hz) {
   return &taps.emplace(key, std::move(dt)).first->second;
 }
 
+void* afe_ctx::prof_event() {
+#if AFE_CUDA
+  if (!prof_free.empty()) { void* e = prof_free.back(); prof_free.pop_back(); return e; }
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+  return e;
+#else
+  return nullptr;
+#endif
+}
+
+namespace afe {
+ProfScope::ProfScope(afe_ctx* ctx, int kernel_id, cudaStream_t stream) : c(ctx), id(kernel_id), s(stream) {
+  std::lock_guard<std::mutex> lock(c->mu);
+  c->prof_launches[id]++;
+#if AFE_CUDA
+  if (c->profiling) {
+    void* e0 = c->prof_event();
+    e1 = c->prof_event();
+    if (e0 && e1) {
+      cudaEventRecord((cudaEvent_t)e0, s);
+      c->prof_recs.push_back({id, e0, e1});
+    } else {
+      e1 = nullptr;
+    }
+  }
+#endif
+}
+ProfScope::~ProfScope() {
+#if AFE_CUDA
+  if (e1) cudaEventRecord((cudaEvent_t)e1, s);
+#endif
+}
+}  // namespace afe
+
 extern "C" {
+
+static const char* kKernelNames[AFE_K_COUNT] = {"resample", "mix_stereo", "fbank", "fbank_stats", "fbank_norm",
+                                                "acoustic_tile", "acoustic_max", "acoustic_mfcc", "acoustic_final"};
+const char* afe_kernel_name(int id) { return (id >= 0 && id < AFE_K_COUNT) ? kKernelNames[id] : "?"; }
+
+int afe_profile_enable(afe_ctx* ctx, int enabled) {
+  if (!ctx) return fail(AFE_ERR_INVALID, "afe_profile_enable: ctx is NULL");
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  ctx->profiling = enabled != 0;
+  return AFE_OK;
+}
+
+int afe_profile_reset(afe_ctx* ctx) {
+  if (!ctx) return fail(AFE_ERR_INVALID, "afe_profile_reset: ctx is NULL");
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  for (auto& r : ctx->prof_recs) { ctx->prof_free.push_back(r.e0); ctx->prof_free.push_back(r.e1); }
+  ctx->prof_recs.clear();
+  for (int i = 0; i < AFE_K_COUNT; ++i) ctx->prof_launches[i] = 0;
+  return AFE_OK;
+}
+
+int afe_profile_read(afe_ctx* ctx, double* h_ms, int64_t* h_launches) {
+  if (!ctx || !h_ms || !h_launches) return fail(AFE_ERR_INVALID, "afe_profile_read: NULL argument");
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  for (int i = 0; i < AFE_K_COUNT; ++i) { h_ms[i] = 0.0; h_launches[i] = ctx->prof_launches[i]; }
+#if AFE_CUDA
+  for (auto& r : ctx->prof_recs) {
+    if (cudaEventSynchronize((cudaEvent_t)r.e1) != cudaSuccess) return fail(AFE_ERR_CUDA, "afe_profile_read: event sync failed");
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, (cudaEvent_t)r.e0, (cudaEvent_t)r.e1) != cudaSuccess)
+      return fail(AFE_ERR_CUDA, "afe_profile_read: elapsed time failed");
+    h_ms[r.id] += (double)ms;
+  }
+#endif
+  return AFE_OK;
+}
 
 const char* afe_version(void) { return "afe-b200 0.1.0"; }
 int afe_backend(void) { return AFE_CUDA ? 1 : 2; }
@@ -164,6 +235,10 @@ int afe_create(int device, afe_ctx** out) {
 void afe_destroy(afe_ctx* c) {
   if (!c) return;
   for (void* p : c->owned) dev_free(p);
+#if AFE_CUDA
+  for (auto& r : c->prof_recs) { cudaEventDestroy((cudaEvent_t)r.e0); cudaEventDestroy((cudaEvent_t)r.e1); }
+  for (void* e : c->prof_free) cudaEventDestroy((cudaEvent_t)e);
+#endif
   for (auto& b : c->staging) {
 #if AFE_CUDA
     if (b.event) cudaEventDestroy((cudaEvent_t)b.event);

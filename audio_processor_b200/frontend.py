@@ -43,6 +43,7 @@ class CallFrontend:
         self.padding_value = float(padding_value)
         self.precision = precision
         self.acoustic = acoustic
+        self._tables = {}
 
     def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True
                       ) -> FrontendResult:
@@ -51,7 +52,7 @@ class CallFrontend:
         res = FrontendResult(n_calls=len(calls))
         chunk_samples = int(self.chunk_duration_sec * sr_t)
         step = chunk_samples - int(self.overlap_sec * sr_t)
-        mixed_l, agent_l, client_l = [], [], []
+        mixed_p, agent_p, client_p, lens = [], [], [], []
         for ci, call in enumerate(calls):
             res.call_seconds += call.shape[1] / float(sample_rate)
             x = call.to(self.device, non_blocking=True)
@@ -61,26 +62,37 @@ class CallFrontend:
                 else:
                     y = fe.resample(x, sample_rate, sr_t); mixed = y
             else:
-                y = x; mixed = fe.mix_stereo(x) if x.shape[0] == 2 else x
+                y = x.contiguous(); mixed = fe.mix_stereo(y) if y.shape[0] == 2 else y
             res.waveforms.append((y, mixed))
-            agent, client = (y[0], y[1]) if y.shape[0] == 2 else (y[0], y[0])
-            for idx, (s, e) in enumerate(chunk_table(y.shape[1], chunk_samples, step)):
+            Lr = int(y.shape[1])
+            pa = y.data_ptr()
+            pc = pa + 4 * Lr if y.shape[0] == 2 else pa
+            pm = mixed.data_ptr()
+            for idx, (s, e) in enumerate(self._chunk_table(Lr, chunk_samples, step)):
                 res.chunks.append((ci, idx, s, e))
-                mixed_l.append(mixed[0, s:e]); agent_l.append(agent[s:e]); client_l.append(client[s:e])
+                mixed_p.append(pm + 4 * s); agent_p.append(pa + 4 * s); client_p.append(pc + 4 * s); lens.append(e - s)
         n = len(res.chunks)
         if n == 0:
             return res
         # transcribe_batch: stable sort by mixed length, slices of batch_size
-        res.order = sorted(range(n), key=lambda i: res.chunks[i][3] - res.chunks[i][2])
-        for key, lst in (("stereo", mixed_l), ("agent", agent_l), ("client", client_l)):
-            res.features[key] = fe.fbank([lst[i] for i in res.order], padding_value=self.padding_value,
-                                         precision=self.precision, group_size=self.batch_size)
+        res.order = sorted(range(n), key=lens.__getitem__)
+        slens = [lens[i] for i in res.order]
+        for key, lst in (("stereo", mixed_p), ("agent", agent_p), ("client", client_p)):
+            res.features[key] = fe.fbank_ptrs([lst[i] for i in res.order], slens, padding_value=self.padding_value,
+                                              precision=self.precision, group_size=self.batch_size)
         if self.acoustic:
-            rows, status = fe.acoustic(agent_l + client_l, sr_t)
+            rows, status = fe.acoustic_ptrs(agent_p + client_p, lens + lens, sr_t)
             if acoustic_to_host:
                 rows = rows.cpu(); status = status.cpu()
             res.acoustic_rows, res.acoustic_status = rows, status
         return res
+
+    def _chunk_table(self, total: int, chunk: int, step: int):
+        key = (total, chunk, step)
+        tab = self._tables.get(key)
+        if tab is None:
+            tab = self._tables[key] = chunk_table(total, chunk, step)
+        return tab
 
     def acoustic_dicts(self, res: FrontendResult):
         """Finish the host side of the acoustic rows: (agent dicts, client dicts) per chunk."""

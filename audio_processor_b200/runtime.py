@@ -57,6 +57,13 @@ class Frontend:
             self._tls.ws = ws
         return ws
 
+    def _workspace2(self, nbytes: int) -> torch.Tensor:
+        ws = getattr(self._tls, "ws2", None)        # the acoustic workspace (holds the mel-dB rows)
+        if ws is None or ws.numel() < nbytes:
+            ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
+            self._tls.ws2 = ws
+        return ws
+
     def _to_device_1d(self, waves: Sequence[Wave]) -> Tuple[List[torch.Tensor], List[int]]:
         """Mono float32 device views of every waveform; host inputs share ONE pinned staging
         buffer and ONE H2D copy (offsets rounded to 4 floats so rows stay 16-byte aligned)."""
@@ -128,7 +135,16 @@ class Frontend:
         (B, Tp/2) int32) on the device.  With ``group_size`` > 0 several processor() calls are
         featurised in one launch and a list of (features, mask) per group is returned."""
         dev_waves, lens = self._to_device_1d(waves)
-        B = len(dev_waves)
+        out = self.fbank_ptrs([t.data_ptr() if t.numel() else 0 for t in dev_waves], lens, padding_value,
+                              precision, raw, group_size)
+        self._tls.keep = dev_waves                  # stream-ordered lifetime of the staged inputs
+        return out
+
+    def fbank_ptrs(self, ptrs: Sequence[int], lens: Sequence[int], padding_value: float = 0.0,
+                   precision: int = _native.PRECISION_F64, raw: bool = False, group_size: int = 0):
+        """Same as ``fbank`` for waveforms already on this device, given as raw device addresses
+        (float32, contiguous) and sample counts -- no per-waveform tensor objects."""
+        B = len(ptrs)
         G = int(group_size) if group_size and group_size > 0 else 0
         if B == 0:
             empty = (torch.empty((0, 0, 160), dtype=torch.float32, device=self.device),
@@ -143,13 +159,11 @@ class Frontend:
         feat = torch.empty((half, 160), dtype=torch.float32, device=self.device)
         mask = torch.empty((half,), dtype=torch.int32, device=self.device)
         ws = self._workspace(int(self.lib.afe_fbank_workspace_bytes(lens_c, B)))
-        ptrs = _native.ptr_array([t.data_ptr() if t.numel() else 0 for t in dev_waves])
         with torch.cuda.device(self.device):
             self.lib.check(self.lib.afe_fbank_batch(
-                self.ctx, self._stream(), ptrs, lens_c, B, G, float(padding_value), int(precision),
+                self.ctx, self._stream(), _native.ptr_array(ptrs), lens_c, B, G, float(padding_value), int(precision),
                 _native.FBANK_RAW if raw else 0, C.c_void_p(feat.data_ptr()), C.c_void_p(mask.data_ptr()),
                 C.c_void_p(ws.data_ptr()), ws.numel()))
-        self._tls.keep = dev_waves                  # stream-ordered lifetime of the staged inputs
         out, r = [], 0
         for g in range(ng):
             n = min(G, B - g * G) if G else B
@@ -162,17 +176,32 @@ class Frontend:
     def acoustic(self, waves: Sequence[Wave], sample_rate: int = 16000) -> Tuple[torch.Tensor, torch.Tensor]:
         """((B, 38) float32 feature rows, (B,) int32 status) on the device; see afe.h."""
         dev_waves, lens = self._to_device_1d(waves)
-        B = len(dev_waves)
+        out = self.acoustic_ptrs([t.data_ptr() if t.numel() else 0 for t in dev_waves], lens, sample_rate)
+        self._tls.keep = dev_waves
+        return out
+
+    def acoustic_ptrs(self, ptrs: Sequence[int], lens: Sequence[int], sample_rate: int = 16000):
+        B = len(ptrs)
         out = torch.empty((B, 38), dtype=torch.float32, device=self.device)
         status = torch.empty((B,), dtype=torch.int32, device=self.device)
         if B == 0:
             return out, status
         lens_c = _native.i64_array(lens)
-        ws = self._workspace(int(self.lib.afe_acoustic_workspace_bytes(lens_c, B)))
-        ptrs = _native.ptr_array([t.data_ptr() if t.numel() else 0 for t in dev_waves])
+        ws = self._workspace2(int(self.lib.afe_acoustic_workspace_bytes(lens_c, B)))
         with torch.cuda.device(self.device):
             self.lib.check(self.lib.afe_acoustic_batch(
-                self.ctx, self._stream(), ptrs, lens_c, B, int(sample_rate), C.c_void_p(out.data_ptr()),
-                C.c_void_p(status.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel()))
-        self._tls.keep = dev_waves
+                self.ctx, self._stream(), _native.ptr_array(ptrs), lens_c, B, int(sample_rate),
+                C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel()))
         return out, status
+
+    # ------------------------------------------------------------------ per-kernel device timing
+    def profile(self, enabled: bool) -> None:
+        self.lib.check(self.lib.afe_profile_enable(self.ctx, 1 if enabled else 0))
+        self.lib.check(self.lib.afe_profile_reset(self.ctx))
+
+    def profile_read(self):
+        """{kernel name: (summed device ms, launches)} since the last ``profile()`` call."""
+        ms = (C.c_double * _native.K_COUNT)()
+        n = (C.c_int64 * _native.K_COUNT)()
+        self.lib.check(self.lib.afe_profile_read(self.ctx, ms, n))
+        return {self.lib.afe_kernel_name(i).decode(): (float(ms[i]), int(n[i])) for i in range(_native.K_COUNT)}

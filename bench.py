@@ -1,0 +1,267 @@
+#!/usr/bin/env python
+"""Headline benchmark: audio-hours/sec through the waveform front end.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo (CUDA, sm_100a)
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path
+
+One STEP = the whole front end over one batch of synthetic calls per GPU -- BASELINE.json
+configs[1]: 64 stereo 8 kHz 5-minute calls -> 16 kHz polyphase resample + agent/client/mixed
+split + 25 s chunks with 1 s overlap + fbank for the three streams in length-sorted batches
+of 16 with dynamic padding + the 38 acoustic features of every agent and client chunk.
+Multi-GPU: calls shard by file across ranks, no collective on the data path (weak scaling).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "audio_hours_per_sec"
+UNIT = "audio-hours/s"
+FBANK_BYTES_PER_FRAME = 962.0          # 640 B new samples + 320 B features + 2 B mask
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="afe", choices=["afe", "reference"])
+    ap.add_argument("--calls", type=int, default=64, help="calls per GPU per step")
+    ap.add_argument("--call-seconds", type=float, default=300.0)
+    ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic calls generated (cycled)")
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"cfg2: {a.calls} stereo 8 kHz {a.call_seconds:.0f} s calls per GPU per step -> resample 16 kHz + split + "
+            f"25 s/1 s chunks + fbank x3 streams (batches of 16, dynamic padding) + 38 acoustic features x2 speakers")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def run_reference(a):
+    """The reference's CPU implementation of the path (oracle/libref: same torchaudio /
+    transformers / torch calls) on the host cores, bounded sample per step."""
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    from oracle import libref
+    cores = os.cpu_count() or 1
+    workers = max(1, min(cores, 64))
+    vals, walls = [], []
+    desc = ""
+    for i in range(a.warmup + a.steps):
+        v, wall, desc = libref.timed_sample(workers, calls_per_worker=3, seconds=60.0)
+        if i >= a.warmup:
+            vals.append(v); walls.append(wall)
+        if sum(walls) > 240:
+            break
+    value = sum(vals) / len(vals)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
+            "steps": len(vals), "warmup": a.warmup, "ms_per_step": 1e3 * sum(walls) / len(walls),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "sample": desc},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port", "sample": desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
+
+
+def ncu_traffic():
+    """Per-launch DRAM bytes of the fbank kernel from the committed ncu summary, if any."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "fbank_ncu_summary.json")) as f:
+            return json.load(f).get("dram_bytes_per_frame")
+    except Exception:
+        return None
+
+
+def run_afe(a):
+    import torch
+    import torch.distributed as dist
+    from audio_processor_b200 import _native, synth
+    from audio_processor_b200.frontend import CallFrontend
+
+    rank, local_rank, world = dist_env()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # synthetic calls: `distinct` seeded calls per rank, cycled; host copies pinned
+    m = max(1, min(a.distinct, a.calls))
+    pool = [synth.make_call(a.call_seconds, 8000, 100 + rank * 1000 + i, 2).pin_memory() for i in range(m)]
+    host_calls = [pool[i % m] for i in range(a.calls)]
+    dev_pool = [c.to(dev) for c in pool]
+    dev_calls = [dev_pool[i % m] for i in range(a.calls)]
+    prec = _native.PRECISION_F64 if a.precision == "f64" else _native.PRECISION_F32
+    cf = CallFrontend(dev, precision=prec)
+    fe = cf.fe
+    audio_hours_per_step = a.calls * a.call_seconds / 3600.0
+
+    for _ in range(max(a.warmup, 3)):
+        r = cf.process_calls(dev_calls, 8000, acoustic_to_host=False)
+    n_chunks = len(r.chunks)
+    frames_per_stream = sum(1 + (e - s - 400) // 160 for _, _, s, e in r.chunks if e - s >= 400)
+    del r
+    torch.cuda.synchronize(dev)
+
+    # ---- timed region A: inputs resident in HBM ------------------------------------------
+    sampler = ClockSampler(local_rank)
+    fe.profile(True)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        r = cf.process_calls(dev_calls, 8000, acoustic_to_host=False)
+        del r
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_dev = e0.elapsed_time(e1)
+    prof = fe.profile_read()
+    fe.profile(False)
+
+    # ---- timed region B: end to end from pinned host buffers -----------------------------
+    for _ in range(2):
+        r = cf.process_calls(host_calls, 8000, acoustic_to_host=True)
+    del r
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    f0.record()
+    checksum = 0.0
+    for _ in range(a.steps):
+        r = cf.process_calls(host_calls, 8000, acoustic_to_host=True)
+        checksum += float(r.acoustic_rows[:, 0].sum())        # the step's host-side result is consumed
+        del r
+    f1.record()
+    barrier()
+    ms_e2e = max(f0.elapsed_time(f1), 1e3 * (time.perf_counter() - t0))
+
+    times = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms_dev, ms_e2e = float(times[0]), float(times[1])
+
+    if rank == 0:
+        total_hours = audio_hours_per_step * a.steps * world
+        value = total_hours / (ms_dev / 1e3)
+        e2e_value = total_hours / (ms_e2e / 1e3)
+        fb_ms, fb_n = prof["fbank"]
+        peak, peak_src = measured_peak()
+        frames_per_launch = frames_per_stream            # one launch per stream
+        achieved = frames_per_launch * FBANK_BYTES_PER_FRAME / (fb_ms / max(fb_n, 1) * 1e-3) / 1e9 if fb_ms > 0 else None
+        traffic_pf = ncu_traffic()
+        kernel_ms = {k: round(v[0] / a.steps, 4) for k, v in prof.items() if v[1]}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if a.precision == "f64" else "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "calls_per_gpu": a.calls, "call_seconds": a.call_seconds,
+                       "chunks_per_step_per_gpu": n_chunks, "distinct_calls": m, "parallelism": f"dp{world} by file",
+                       "l2": "inputs (1.2 GB/step) larger than L2; no flush needed",
+                       "fbank_precision": a.precision, "kernel_ms_per_step": kernel_ms},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps,
+                    "h2d_bytes_per_step": int(a.calls * 2 * a.call_seconds * 8000 * 4),
+                    "d2h_bytes_per_step": int(2 * n_chunks * (38 * 4 + 4)), "checksum": checksum},
+            "gpu_launches": int(sum(v[1] for v in prof.values())),
+            "roofline": {"bound": "hbm", "kernel": "phased_kernel<FbankKernel<%s>>" % ("double" if a.precision == "f64" else "float"),
+                         "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": (achieved / peak) if achieved else None,
+                         "traffic": (traffic_pf * frames_per_launch) if traffic_pf else None,
+                         "algorithmic_bytes_per_launch": frames_per_launch * FBANK_BYTES_PER_FRAME,
+                         "launches_timed": fb_n, "avg_launch_ms": fb_ms / max(fb_n, 1),
+                         "note": "fp64-issue-bound, not HBM-bound: see DESIGN.md section 5"},
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            from oracle import libref
+            cores = os.cpu_count() or 1
+            v, wall, desc = libref.timed_sample(max(1, min(cores, 64)), calls_per_worker=3, seconds=60.0)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": max(1, min(cores, 64)), "kind": "port",
+                                    "sample": desc, "wall_s": wall}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_afe(a)
+
+
+if __name__ == "__main__":
+    main()

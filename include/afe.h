@@ -113,6 +113,19 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
                        int batch, int sample_rate, float* d_out, int32_t* d_status,
                        void* d_workspace, size_t workspace_bytes);
 
+/* ---- per-kernel device timing (CUDA events on the caller's stream) --------------------
+ * While enabled every kernel launch of this context is bracketed by cudaEvents.
+ * afe_profile_read synchronises those events and returns, per kernel id, the summed device
+ * time in milliseconds and the number of launches since the last reset. */
+enum {
+  AFE_K_RESAMPLE = 0, AFE_K_MIX = 1, AFE_K_FBANK = 2, AFE_K_FBANK_STATS = 3, AFE_K_FBANK_NORM = 4,
+  AFE_K_AC_TILE = 5, AFE_K_AC_MAX = 6, AFE_K_AC_MFCC = 7, AFE_K_AC_FINAL = 8, AFE_K_COUNT = 9
+};
+int afe_profile_enable(afe_ctx* ctx, int enabled);
+int afe_profile_reset(afe_ctx* ctx);
+int afe_profile_read(afe_ctx* ctx, double* h_ms /*[AFE_K_COUNT]*/, int64_t* h_launches /*[AFE_K_COUNT]*/);
+const char* afe_kernel_name(int kernel_id);
+
 #ifdef __cplusplus
 }
 #endif
