@@ -39,7 +39,7 @@ AcLayout ac_layout(const int64_t* lengths, int B) {
   l.desc_bytes = o;
   l.off_tile = align_up(o, 256);
   l.off_mfcc = align_up(l.off_tile + sizeof(double) * kTileRec * (size_t)l.ntiles, 256);
-  l.off_bound = align_up(l.off_mfcc + sizeof(double) * 2 * kMfcc * (size_t)l.ntiles, 256);
+  l.off_bound = align_up(l.off_mfcc + sizeof(double) * 2 * 14 * (size_t)l.ntiles, 256);
   l.off_gmax = align_up(l.off_bound + sizeof(float) * 2 * kBoundary * (size_t)l.ntiles, 256);
   l.off_meldb = align_up(l.off_gmax + sizeof(float) * (size_t)B, 256);
   l.total = align_up(l.off_meldb + sizeof(float) * kAcMel * (size_t)l.rows, 256);
@@ -109,8 +109,7 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
 
   AcousticTileKernel tk;
   tk.d = d; tk.hann = ctx->d_hann32; tk.tw512 = ctx->d_tw32;
-  tk.mel_start = ctx->d_htk_start; tk.mel_count = ctx->d_htk_count; tk.mel_offset = ctx->d_htk_offset;
-  tk.mel_w = ctx->d_htk_w; tk.meldb = meldb; tk.tile_rec = tile_rec; tk.boundary = boundary;
+  tk.meldb = meldb; tk.tile_rec = tile_rec; tk.boundary = boundary;
   int rc;
   { ProfScope ps(ctx, AFE_K_AC_TILE, s); rc = afe_launch(tk, AcSmem::kBytes, ctx->num_sms, s); }
   if (rc == 0) {
@@ -119,7 +118,7 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
     rc = afe_launch(mk, 0, 1 << 20, s);
   }
   if (rc == 0) {
-    AcousticMfccKernel ck{d, meldb, gmax, ctx->d_dct, mfcc_rec};
+    AcousticMfccKernel ck{d, meldb, gmax, ctx->d_dct, boundary, mfcc_rec};
     ProfScope ps(ctx, AFE_K_AC_MFCC, s);
     rc = afe_launch(ck, AcousticMfccKernel::kSmemBytes, ctx->num_sms * 4, s);
   }

@@ -41,63 +41,93 @@ AFE_HD void ac_locate(const AcDesc& d, long item, int& b, int& t) {
   t = (int)(item - ldg(d.tile_prefix + lo));
 }
 
+constexpr int kHtkIv = kAcMel + 1;                // 129 intervals
+
 struct AcSmem {
-  // region A: raw + padded copy, later the magnitudes sM[257][32]
-  static constexpr size_t kRawOff = 0;                                           // float[5568]
-  static constexpr size_t kDOff = kRawOff + sizeof(float) * kAcRaw;              // float[5536]
-  static constexpr size_t kABytes = sizeof(float) * (kAcRaw + 5536);             // 44416 >= 32896
-  static constexpr size_t kSmallOff = kABytes;
-  //   small arrays (floats): sq16[336] zc16[336] lastx[32] parts_e[512] parts_c[512] red[512] pf[8][32]
-  static constexpr int kSq = 0, kZc = 336, kLast = 672, kPe = 704, kPc = 1216, kRed = 1728, kPf = 2240;
-  static constexpr size_t kSmallBytes = sizeof(float) * (2240 + 8 * 32);
-  static constexpr size_t kPOff = (kSmallOff + kSmallBytes + 15) / 16 * 16;      // float sP[257*32]
+  static constexpr size_t kRawBytes = sizeof(float) * kAcRaw;                    // 22272 per staging buffer
+  static constexpr size_t kRawOff = 0;                                           // float[2][5568]
+  static constexpr size_t kDOff = kRawOff + 2 * kRawBytes;                       // float[5536] padded copy
+  static constexpr size_t kSmallOff = kDOff + sizeof(float) * 5536;
+  // small arrays, in floats from kSmallOff (epart is double[512], 8-byte aligned)
+  static constexpr int kEp = 0;            // double[16][32] contiguous-range magnitude sums
+  static constexpr int kSq = 1024, kZc = 1360, kLast = 1696;        // [336] [336] [32]
+  static constexpr int kPc = 1728, kRed = 2240, kCnt = 2752, kBw = 3264, kFx = 3776;   // [512] each
+  static constexpr int kPf = 4288;         // [8][32] per-frame scalars
+  static constexpr size_t kSmallBytes = sizeof(float) * (4288 + 8 * 32);
+  static constexpr size_t kPOff = (kSmallOff + kSmallBytes + 15) / 16 * 16;      // float sP[257*32] -> magnitudes in place
   static constexpr size_t kExOff = (kPOff + sizeof(float) * kBins * kTileFrames + 15) / 16 * 16;
-  static constexpr size_t kBytes = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // ex | sDb[32][129]
+  //   ex region after stage 2: sU[129][32] sD[129][32] sDb[32][129]
+  static constexpr size_t kDbOff = kExOff + sizeof(float) * 2 * kHtkIv * kTileFrames;
+  static constexpr size_t kBytes = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;
+  static_assert(kDbOff + sizeof(float) * kTileFrames * kDbStride <= kBytes, "ex region too small");
 };
 
 struct AcousticTileKernel {
   static constexpr int kThreads = 512;
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 7;
+  static constexpr int kPhases = 9;
+  static constexpr bool kAsyncStage = true;
+  static constexpr size_t kStageOff = AcSmem::kRawOff;
+  static constexpr size_t kStageBytes = AcSmem::kRawBytes;
+
+  struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int F1; int64_t L; const float* wave; int64_t row0; };
 
   AcDesc d;
   const float* hann;        // [400] periodic Hann / 2
   const float* tw512;       // [16][16][2]
-  const int32_t* mel_start; const int32_t* mel_count; const int32_t* mel_offset; const float* mel_w;
   float* meldb;             // [rows][128]
   double* tile_rec;         // [ntiles][16]
   float* boundary;          // [ntiles][2][260]  first / last valid frame magnitudes
 
   AFE_HD long num_items() const { return d.ntiles; }
 
-  AFE_HD void phase(int ph, long item, unsigned char* smem, int tid) const {
-    float* raw = reinterpret_cast<float*>(smem + AcSmem::kRawOff);
+  AFE_HD Item prepare(long item) const {
+    Item it;
+    int t;
+    ac_locate(d, item, it.b, t);
+    it.item = item; it.buf = 0; it.bulk = 0;
+    it.f0 = t * kTileFrames;
+    it.nvalid = tmin(kTileFrames, ldg(d.frames2 + it.b) - it.f0);
+    it.F1 = ldg(d.frames1 + it.b);
+    it.L = ldg(d.len + it.b);
+    it.wave = ldg(d.wave + it.b);
+    it.row0 = ldg(d.row_prefix + it.b);
+    return it;
+  }
+  // interior tiles (no reflection) are one contiguous aligned copy
+  AFE_HD bool stage_src(const Item& it, const float*& src, int& nfloats) const {
+    const int64_t g0 = (int64_t)it.f0 * kHop - 200;
+    src = it.wave + g0; nfloats = kAcRaw;
+    return g0 >= 0 && g0 + kAcRaw <= it.L && (reinterpret_cast<uintptr_t>(src) & 15u) == 0;
+  }
+
+  AFE_HD static bool crossing(float a, float c) { return (a > 0.f && c < 0.f) || (a < 0.f && c > 0.f); }
+
+  AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
+    float* raw = reinterpret_cast<float*>(smem + AcSmem::kRawOff + (size_t)it.buf * AcSmem::kRawBytes);
     float* dbuf = reinterpret_cast<float*>(smem + AcSmem::kDOff);
-    float* sM = reinterpret_cast<float*>(smem + AcSmem::kRawOff);
     float* small = reinterpret_cast<float*>(smem + AcSmem::kSmallOff);
-    float* sP = reinterpret_cast<float*>(smem + AcSmem::kPOff);
+    float* sP = reinterpret_cast<float*>(smem + AcSmem::kPOff);        // power, then magnitude in place
     cplx<float>* ex = reinterpret_cast<cplx<float>*>(smem + AcSmem::kExOff);
-    float* sDb = reinterpret_cast<float*>(smem + AcSmem::kExOff);
+    float* sU = reinterpret_cast<float*>(smem + AcSmem::kExOff);
+    float* sD = sU + kHtkIv * kTileFrames;
+    float* sDb = reinterpret_cast<float*>(smem + AcSmem::kDbOff);
+    double* epart = reinterpret_cast<double*>(small + AcSmem::kEp);
     float* sq16 = small + AcSmem::kSq;  float* zc16 = small + AcSmem::kZc;  float* lastx = small + AcSmem::kLast;
-    float* pe = small + AcSmem::kPe;    float* pc = small + AcSmem::kPc;    float* red = small + AcSmem::kRed;
-    float* pf = small + AcSmem::kPf;    // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
-    int b, t;
-    ac_locate(d, item, b, t);
-    const int64_t L = ldg(d.len + b);
-    const int F1 = ldg(d.frames1 + b), F2 = ldg(d.frames2 + b);
-    const int f0 = t * kTileFrames;
-    const int nvalid = tmin(kTileFrames, F2 - f0);
+    float* pc = small + AcSmem::kPc;    float* red = small + AcSmem::kRed;
+    float* cntp = small + AcSmem::kCnt; float* bwp = small + AcSmem::kBw;   float* fxp = small + AcSmem::kFx;
+    float* pf = small + AcSmem::kPf;    // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax [7]=energy
     const int role = tid >> 5, f = tid & 31;
+    const int kb = role * 16, ke = (role == 15) ? kBins : kb + 16;       // contiguous bin range of this role
 
     switch (ph) {
-      case 0: {   // stage y[reflect(160 f0 - 200 + i)]
-        const float* src = ldg(d.wave + b);
-        const int64_t g0 = (int64_t)f0 * kHop - 200;
+      case 0: {   // stage y[reflect(160 f0 - 200 + i)] (edge tiles; interior tiles arrive by TMA)
+        const int64_t g0 = (int64_t)it.f0 * kHop - 200;
         for (int i = tid; i < kAcRaw; i += kThreads) {
           int64_t g = g0 + i;
           if (g < 0) g = -g;
-          if (g >= L) g = 2 * (L - 1) - g;
-          raw[i] = (g >= 0 && g < L) ? src[g] : 0.f;
+          if (g >= it.L) g = 2 * (it.L - 1) - g;
+          raw[i] = (g >= 0 && g < it.L) ? it.wave[g] : 0.f;
         }
       } break;
       case 1: {   // padded copy for the STFT + 16-sample partials of the unfold frames
@@ -106,16 +136,15 @@ struct AcousticTileKernel {
           float s = 0.f, z = 0.f;
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const float a = raw[200 + tid * 16 + j], c = raw[200 + tid * 16 + j + 1];
+            const int i = 200 + tid * 16 + ((j + tid) & 15);           // rotated: 2-way bank conflicts
+            const float a = raw[i], c = raw[i + 1];
             s = fma_f(a, a, s);
-            z += ((a > 0.f && c < 0.f) || (a < 0.f && c > 0.f)) ? 1.f : 0.f;
+            z += crossing(a, c) ? 1.f : 0.f;
           }
           sq16[tid] = s; zc16[tid] = z;
         }
-        if (tid < kTileFrames) {   // the pair (399, 400) of unfold frame tid is NOT part of the frame
-          const float a = raw[200 + kHop * tid + 399], c = raw[200 + kHop * tid + 400];
-          lastx[tid] = ((a > 0.f && c < 0.f) || (a < 0.f && c > 0.f)) ? 1.f : 0.f;
-        }
+        if (tid < kTileFrames)     // the pair (399, 400) of unfold frame tid is NOT part of the frame
+          lastx[tid] = crossing(raw[200 + kHop * tid + 399], raw[200 + kHop * tid + 400]) ? 1.f : 0.f;
       } break;
       case 2: {   // Hann window + stage 1 of the real FFT
         float r[25];
@@ -129,73 +158,84 @@ struct AcousticTileKernel {
       case 3:
         rfft512_stage2<float>(role, f, ex, sP);
         break;
-      case 4: {   // magnitudes, energy / first-moment partials, 128 HTK mel -> dB
-        float e = 0.f, c = 0.f;
-        for (int k = role; k < kBins; k += kRoles) {
-          const float m = fast_sqrt(sP[k * kTileFrames + f]);
-          sM[k * kTileFrames + f] = m;
-          e += m; c = fma_f(m, (float)k, c);
-        }
-        pe[role * 32 + f] = e; pc[role * 32 + f] = c;
+      case 4:     // 128 HTK mel filters, interval form (reads the POWER spectrum)
+        mel_intervals_htk(role, f, sP, sU, sD);
+        break;
+      case 5: {   // dB rows; magnitudes in place + contiguous-range sums
         float mx = -3.0e38f;
-#pragma unroll 1
+#pragma unroll
         for (int m = role; m < kAcMel; m += kRoles) {
-          const int k0 = ldg(mel_start + m), cnt = ldg(mel_count + m), off = ldg(mel_offset + m);
-          float acc = 0.f;
-          for (int i = 0; i < cnt; ++i) acc = fma_f(ldg(mel_w + off + i), sP[(k0 + i) * kTileFrames + f], acc);
+          const float acc = sU[m * kTileFrames + f] + sD[(m + 1) * kTileFrames + f];
           const float db = 10.f * fast_log10(tmax(acc, 1e-10f));
           sDb[f * kDbStride + m] = db;
           mx = tmax(mx, db);
         }
         red[tid] = mx;
+        double e = 0.0;
+        float c = 0.f;
+        for (int k = kb; k < ke; ++k) {
+          const float m = fast_sqrt(sP[k * kTileFrames + f]);
+          sP[k * kTileFrames + f] = m;
+          e += (double)m; c = fma_f(m, (float)k, c);
+        }
+        epart[role * 32 + f] = e; pc[role * 32 + f] = c;
       } break;
-      case 5: {   // per-frame scalars, one role each
-        if (role == 0 || role == 2) {
-          float e = 0.f, c = 0.f;
+      case 6: {   // per-frame totals, then this role's share of rolloff / bandwidth / flux
+        double tot = 0.0, pre = 0.0;
+        float c = 0.f;
 #pragma unroll
-          for (int r = 0; r < kRoles; ++r) { e += pe[r * 32 + f]; c += pc[r * 32 + f]; }
-          const float energy = e + 1e-8f;
-          const float cen = 31.25f * c / energy;
-          if (role == 0) {
-            pf[0 * 32 + f] = cen;
-            double acc = 0.0;
-            for (int k = 0; k < kBins; ++k) acc += (double)sM[k * kTileFrames + f];
-            const float thr = 0.85f * ((float)acc + 1e-8f);
-            acc = 0.0;
-            int below = 0;
-            for (int k = 0; k < kBins; ++k) { acc += (double)sM[k * kTileFrames + f]; below += ((float)acc < thr) ? 1 : 0; }
-            pf[2 * 32 + f] = 31.25f * (float)(below >= kBins ? 0 : below);
-          } else {
-            float s = 0.f;
-            for (int k = 0; k < kBins; ++k) {
-              const float df = 31.25f * (float)k - cen;
-              s = fma_f(sM[k * kTileFrames + f], df * df, s);
-            }
-            pf[1 * 32 + f] = fast_sqrt(s / energy);
-          }
-        } else if (role == 1) {
-          float s = 0.f;
-          if (f + 1 < nvalid)
-            for (int k = 0; k < kBins; ++k) s += tmax(sM[k * kTileFrames + f + 1] - sM[k * kTileFrames + f], 0.f);
-          pf[3 * 32 + f] = s;
-        } else if (role == 3) {
+        for (int r = 0; r < kRoles; ++r) {
+          if (r == role) pre = tot;
+          tot += epart[r * 32 + f]; c += pc[r * 32 + f];
+        }
+        const float total = (float)tot;                  // cum_energy[-1] (float64 accumulate like ATen's cumsum)
+        const float energy = total + 1e-8f;
+        const float cen = 31.25f * c / energy;
+        const float thr = 0.85f * (total + 1e-8f);
+        double acc = pre;
+        int below = 0;
+        float bw = 0.f, fx = 0.f;
+        const bool has_next = (f + 1 < it.nvalid);
+        for (int k = kb; k < ke; ++k) {
+          const float m = sP[k * kTileFrames + f];
+          acc += (double)m;
+          below += ((float)acc < thr) ? 1 : 0;
+          const float df = 31.25f * (float)k - cen;
+          bw = fma_f(m, df * df, bw);
+          if (has_next) fx += tmax(sP[k * kTileFrames + f + 1] - m, 0.f);
+        }
+        cntp[role * 32 + f] = (float)below; bwp[role * 32 + f] = bw; fxp[role * 32 + f] = fx;
+        if (role == 0) { pf[0 * 32 + f] = cen; pf[7 * 32 + f] = energy; }
+        if (role == 1) {
           float s = 0.f, z = 0.f;
 #pragma unroll
           for (int g = 0; g < 25; ++g) { s += sq16[10 * f + g]; z += zc16[10 * f + g]; }
           pf[4 * 32 + f] = fast_sqrt(s / 400.f);
           pf[5 * 32 + f] = (z - lastx[f]) / 400.f;
-        } else if (role == 4) {
+        }
+        if (role == 2) {
           float mx = -3.0e38f;
 #pragma unroll
           for (int r = 0; r < kRoles; ++r) mx = tmax(mx, red[r * 32 + f]);
           pf[6 * 32 + f] = mx;
         }
       } break;
-      case 6: {   // tile record, boundary spectra, mel-dB rows
-        double* rec = tile_rec + item * kTileRec;
+      case 7: {   // combine the 16 partials per frame
+        if (role < 3) {
+          float s = 0.f;
+          const float* src = (role == 0) ? cntp : (role == 1) ? bwp : fxp;
+#pragma unroll
+          for (int r = 0; r < kRoles; ++r) s += src[r * 32 + f];
+          if (role == 0) pf[2 * 32 + f] = 31.25f * ((s >= (float)kBins) ? 0.f : s);
+          else if (role == 1) pf[1 * 32 + f] = fast_sqrt(s / pf[7 * 32 + f]);
+          else pf[3 * 32 + f] = s;
+        }
+      } break;
+      case 8: {   // tile record, boundary spectra, mel-dB rows
+        double* rec = tile_rec + it.item * kTileRec;
         if (tid < 5) {          // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff
           const int src = (tid == 0) ? 4 : (tid == 1) ? 5 : (tid - 2);
-          const int n = (tid < 2) ? tmax(0, tmin(kTileFrames, F1 - f0)) : nvalid;
+          const int n = (tid < 2) ? tmax(0, tmin(kTileFrames, it.F1 - it.f0)) : it.nvalid;
           double s = 0.0, ss = 0.0, mn = 3.0e38, mxv = -3.0e38;
           for (int j = 0; j < n; ++j) {
             const double v = (double)pf[src * 32 + j];
@@ -205,20 +245,21 @@ struct AcousticTileKernel {
           if (tid == 0) { rec[11] = mn; rec[12] = mxv; }
         } else if (tid == 5) {
           double s = 0.0;
-          for (int j = 0; j + 1 < nvalid; ++j) { const double v = (double)pf[3 * 32 + j]; s += v * v; }
+          for (int j = 0; j + 1 < it.nvalid; ++j) { const double v = (double)pf[3 * 32 + j]; s += v * v; }
           rec[10] = s;
         } else if (tid == 6) {
           float mx = -3.0e38f;
-          for (int j = 0; j < nvalid; ++j) mx = tmax(mx, pf[6 * 32 + j]);
+          for (int j = 0; j < it.nvalid; ++j) mx = tmax(mx, pf[6 * 32 + j]);
           rec[13] = (double)mx;
         }
-        if (tid < kBins) {
-          float* bd = boundary + item * 2 * kBoundary;
-          bd[tid] = sM[tid * kTileFrames + 0];
-          bd[kBoundary + tid] = sM[tid * kTileFrames + (nvalid - 1)];
+        if (tid >= 64 && tid < 64 + kBins) {
+          const int k = tid - 64;
+          float* bd = boundary + it.item * 2 * kBoundary;
+          bd[k] = sP[k * kTileFrames + 0];
+          bd[kBoundary + k] = sP[k * kTileFrames + (it.nvalid - 1)];
         }
-        float* dst = meldb + (ldg(d.row_prefix + b) + f0) * kAcMel;
-        for (int i = tid; i < nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
+        float* dst = meldb + (it.row0 + it.f0) * kAcMel;
+        for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
       } break;
     }
   }
@@ -229,8 +270,10 @@ struct AcousticMaxKernel {
   static constexpr int kMinBlocks = 1;
   static constexpr int kPhases = 1;
   AcDesc d; const double* tile_rec; float* gmax;
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return d.B; }
-  AFE_HD void phase(int, long item, unsigned char*, int tid) const {
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    const long item = it.item;
     if (tid != 0) return;
     double mx = -3.0e38;
     for (long t = ldg(d.tile_prefix + item); t < ldg(d.tile_prefix + item + 1); ++t) {
@@ -245,34 +288,56 @@ struct AcousticMfccKernel {
   static constexpr int kThreads = 512;
   static constexpr int kMinBlocks = 2;
   static constexpr int kPhases = 3;
-  static constexpr size_t kSmemBytes = sizeof(float) * (kTileFrames * kDbStride + 16 * 32);
-  AcDesc d; const float* meldb; const float* gmax; const float* dct; double* mfcc_rec;   // [ntiles][13][2]
+  static constexpr size_t kSmemBytes = sizeof(float) * (kTileFrames * kDbStride + 16 * 32 + 512);
+  AcDesc d; const float* meldb; const float* gmax; const float* dct; const float* boundary;
+  double* mfcc_rec;        // [ntiles][14][2]: 13 x (sum, sum sq) + (boundary flux^2, 0)
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return d.ntiles; }
-  AFE_HD void phase(int ph, long item, unsigned char* smem, int tid) const {
+  AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
+    const long item = it.item;
     float* sD = reinterpret_cast<float*>(smem);
     float* sC = sD + kTileFrames * kDbStride;
+    float* sX = sC + 16 * 32;
     int b, t;
     ac_locate(d, item, b, t);
     const int F2 = ldg(d.frames2 + b);
     const int f0 = t * kTileFrames;
     const int nvalid = tmin(kTileFrames, F2 - f0);
+    const bool has_next = (item + 1 < ldg(d.tile_prefix + b + 1));     // another tile of the same waveform follows
     if (ph == 0) {
       const float cut = ldg(gmax + b) - 80.f;
       const float* src = meldb + (ldg(d.row_prefix + b) + f0) * kAcMel;
       for (int i = tid; i < kTileFrames * kAcMel; i += kThreads)
         sD[(i >> 7) * kDbStride + (i & 127)] = (i < nvalid * kAcMel) ? tmax(src[i], cut) : 0.f;
+      // spectral flux across the tile boundary: relu(first frame of tile+1 - last frame of this tile)
+      float fl = 0.f;
+      if (has_next && tid < kBins) {
+        const float* last = boundary + item * 2 * kBoundary + kBoundary;
+        const float* first = boundary + (item + 1) * 2 * kBoundary;
+        fl = tmax(first[tid] - last[tid], 0.f);
+      }
+      sX[tid] = fl;
     } else if (ph == 1) {
       const int c = tid >> 5, f = tid & 31;
       if (c < kMfcc) {
         float acc = 0.f;
         for (int n = 0; n < kAcMel; ++n) acc = fma_f(sD[f * kDbStride + n], ldg(dct + c * kAcMel + n), acc);
         sC[c * 32 + f] = acc;
+      } else if (c == 13) {          // 16 partial sums of the boundary flux terms
+        float s = 0.f;
+        for (int q = f; q < kBins; q += 32) s += sX[q];
+        sC[13 * 32 + f] = s;
       }
     } else if (tid < kMfcc) {
       double s = 0.0, ss = 0.0;
       for (int j = 0; j < nvalid; ++j) { const double v = (double)sC[tid * 32 + j]; s += v; ss += v * v; }
-      mfcc_rec[(item * kMfcc + tid) * 2] = s;
-      mfcc_rec[(item * kMfcc + tid) * 2 + 1] = ss;
+      mfcc_rec[(item * 14 + tid) * 2] = s;
+      mfcc_rec[(item * 14 + tid) * 2 + 1] = ss;
+    } else if (tid == 13) {
+      float fl = 0.f;
+      for (int j = 0; j < 32; ++j) fl += sC[13 * 32 + j];
+      mfcc_rec[(item * 14 + 13) * 2] = (double)fl * (double)fl;
+      mfcc_rec[(item * 14 + 13) * 2 + 1] = 0.0;
     }
   }
 };
@@ -290,8 +355,10 @@ struct AcousticFinalKernel {
     const double var = (ss - s * m) / (double)(n - 1);          // n == 1 -> 0/0 = NaN like torch.std
     sd = (float)std::sqrt(var < 0.0 ? 0.0 : var);
   }
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return d.B; }
-  AFE_HD void phase(int, long item, unsigned char*, int tid) const {
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    const long item = it.item;
     float* o = out + item * kAcFeat;
     const int F1 = ldg(d.frames1 + item), F2 = ldg(d.frames2 + item);
     if (F2 <= 0) {                                   // 'Audio too short'
@@ -317,21 +384,12 @@ struct AcousticFinalKernel {
       if (tid == 0) o[2] = (float)(mx - mn);
     } else if (tid == 5) {      // spectral-flux energy: in-tile pairs + tile-boundary pairs
       double s = 0.0;
-      for (long t = t0; t < t1; ++t) {
-        s += tile_rec[t * kTileRec + 10];
-        if (t + 1 < t1) {
-          const float* last = boundary + t * 2 * kBoundary + kBoundary;
-          const float* first = boundary + (t + 1) * 2 * kBoundary;
-          float fl = 0.f;
-          for (int k = 0; k < kBins; ++k) fl += tmax(first[k] - last[k], 0.f);
-          s += (double)fl * (double)fl;
-        }
-      }
+      for (long t = t0; t < t1; ++t) s += tile_rec[t * kTileRec + 10] + mfcc_rec[(t * 14 + 13) * 2];
       o[11] = (float)s;
     } else if (tid >= 6 && tid < 6 + kMfcc) {
       const int c = tid - 6;
       double s = 0.0, ss = 0.0;
-      for (long t = t0; t < t1; ++t) { s += mfcc_rec[(t * kMfcc + c) * 2]; ss += mfcc_rec[(t * kMfcc + c) * 2 + 1]; }
+      for (long t = t0; t < t1; ++t) { s += mfcc_rec[(t * 14 + c) * 2]; ss += mfcc_rec[(t * 14 + c) * 2 + 1]; }
       float mean, sd;
       mean_std(s, ss, F2, mean, sd);
       o[12 + 2 * c] = mean; o[13 + 2 * c] = sd;

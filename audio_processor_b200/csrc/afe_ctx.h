@@ -47,6 +47,8 @@ struct afe_ctx {
   float* d_htk_w = nullptr;
   float* d_dct = nullptr;                                       // [13][128]
   float log_floor = 0.f;
+  struct MelDev { const float* up; const float* dn; const int32_t* iv_start; const int32_t* iv_count; const int32_t* role_iv; };
+  MelDev kaldi_mel_dev{}, htk_mel_dev{};
   std::mutex mu;
   std::map<std::pair<int, int>, afe::DeviceTaps> taps;          // (orig, new) -> bank
   std::vector<afe::StagingBlock> staging;

@@ -44,8 +44,9 @@ int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, dou
               const T* window, const T* tw) {
   FbankKernel<T> k;
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
-  k.mel_start = ctx->d_mel_start; k.mel_count = ctx->d_mel_count; k.mel_offset = ctx->d_mel_offset;
-  k.mel_w = ctx->d_mel_w; k.log_floor = ctx->log_floor;
+  const auto& m = ctx->kaldi_mel_dev;
+  k.mel = MelTables{m.up, m.dn, m.iv_start, m.iv_count, m.role_iv};
+  k.log_floor = ctx->log_floor;
   ProfScope ps(ctx, AFE_K_FBANK, s);
   return afe_launch(k, FbankSmem<T>::kBytes, ctx->num_sms, s);
 }

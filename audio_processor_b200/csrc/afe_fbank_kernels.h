@@ -8,6 +8,7 @@
 // frames of one utterance (5360 samples).  Linear path (pre-emphasis, DC removal, window,
 // FFT) in T; power / mel / log in float.
 #pragma once
+#include "afe_mel_gen.h"
 #include "afe_rfft512.h"
 #include "afe_tables.h"
 
@@ -41,72 +42,113 @@ AFE_HD void locate_tile(const BatchDesc& d, long item, int& b, int& t) {
   t = (int)(item - ldg(d.tile_prefix + lo));
 }
 
+// interval-form triangular bank on the device (afe_tables.h SparseBank::up/dn/iv_*)
+struct MelTables {
+  const float* up; const float* dn;               // [257]
+  const int32_t* iv_start; const int32_t* iv_count;   // [F+1]
+  const int32_t* role_iv;                         // [17]
+};
+
+constexpr int kMelIv = kMel + 1;                  // 81 intervals
+
 template <typename T> struct FbankSmem {
-  static constexpr size_t kRawOff = 0;                                              // float[5360]
-  static constexpr size_t kSumOff = kRawOff + sizeof(float) * kTileSamples;         // float[336]
-  static constexpr size_t kDOff = kSumOff + sizeof(float) * 336;                    // T[5528] | sP + sOut
+  static constexpr size_t kRawBytes = sizeof(float) * kTileSamples;                 // 21440 per staging buffer
+  static constexpr size_t kRawOff = 0;                                              // float[2][5360]
+  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double[336]
+  static constexpr size_t kDOff = kSumOff + sizeof(double) * 336;                   // T[5528] | sP + sOut
   static constexpr size_t kDBytesT = sizeof(T) * (kTileSamples + kTileSamples / 32 + 8);
   static constexpr size_t kPBytes = sizeof(float) * (kBins * kTileFrames);          // 32896
   static constexpr size_t kOutBytes = sizeof(float) * (kTileFrames * kOutStride);   // 10368
   static constexpr size_t kDBytes = (kDBytesT > kPBytes + kOutBytes ? kDBytesT : kPBytes + kOutBytes);
-  static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*32]
-  static constexpr size_t kBytes = kExOff + sizeof(cplx<T>) * 16 * 16 * kTileFrames;
+  static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*32] | sU,sD
+  static constexpr size_t kExBytesT = sizeof(cplx<T>) * 16 * 16 * kTileFrames;
+  static constexpr size_t kUDBytes = sizeof(float) * 2 * kMelIv * kTileFrames;      // 20736
+  static constexpr size_t kBytes = kExOff + (kExBytesT > kUDBytes ? kExBytesT : kUDBytes);
 };
 
 template <typename T> struct FbankKernel {
   static constexpr int kThreads = kRoles * kTileFrames;   // 512
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 6;
+  static constexpr int kPhases = 7;
+  static constexpr bool kAsyncStage = true;
+  static constexpr size_t kStageOff = FbankSmem<T>::kRawOff;
+  static constexpr size_t kStageBytes = FbankSmem<T>::kRawBytes;
+
+  struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int count; const float* src; int64_t out_row; };
 
   BatchDesc d;
   float* out;              // [rows][80] raw log-mel lands at its final position
   double* partials;        // [ntiles][80][2]  (sum, sum of squares) per mel bin
   const T* window;         // [400]  povey * 32768 / 2
   const T* tw512;          // [16][16][2]
-  const int32_t* mel_start; const int32_t* mel_count; const int32_t* mel_offset; const float* mel_w;
+  MelTables mel;
   float log_floor;         // float32(log(float64(mel_floor)))
 
   AFE_HD long num_items() const { return d.ntiles; }
 
-  AFE_HD void phase(int ph, long item, unsigned char* smem, int tid) const {
+  AFE_HD Item prepare(long item) const {
+    Item it;
+    int t;
+    locate_tile(d, item, it.b, t);
+    it.item = item; it.buf = 0; it.bulk = 0;
+    it.f0 = t * kTileFrames;
+    it.nvalid = tmin(kTileFrames, ldg(d.frames + it.b) - it.f0);
+    it.count = (it.nvalid - 1) * kHop + kFrame;
+    it.src = ldg(d.wave + it.b) + (int64_t)it.f0 * kHop;
+    it.out_row = ldg(d.out_row + it.b);
+    return it;
+  }
+  // the tile is one contiguous run of `count` samples: a single TMA bulk copy when 16-byte aligned
+  AFE_HD bool stage_src(const Item& it, const float*& src, int& nfloats) const {
+    src = it.src; nfloats = it.count;
+    return (reinterpret_cast<uintptr_t>(it.src) & 15u) == 0;
+  }
+
+  AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     using S = FbankSmem<T>;
-    float* raw = reinterpret_cast<float*>(smem + S::kRawOff);
-    float* sum16 = reinterpret_cast<float*>(smem + S::kSumOff);
+    float* raw = reinterpret_cast<float*>(smem + S::kRawOff + (size_t)it.buf * S::kRawBytes);
+    double* sum16 = reinterpret_cast<double*>(smem + S::kSumOff);
     T* dbuf = reinterpret_cast<T*>(smem + S::kDOff);
     float* sP = reinterpret_cast<float*>(smem + S::kDOff);
     float* sOut = reinterpret_cast<float*>(smem + S::kDOff + S::kPBytes);
     cplx<T>* ex = reinterpret_cast<cplx<T>*>(smem + S::kExOff);
-    int b, t;
-    locate_tile(d, item, b, t);
-    const int T_b = ldg(d.frames + b);
-    const int f0 = t * kTileFrames;
-    const int nvalid = tmin(kTileFrames, T_b - f0);
+    float* sU = reinterpret_cast<float*>(smem + S::kExOff);
+    float* sD = sU + kMelIv * kTileFrames;
     const int role = tid >> 5, f = tid & 31;
 
     switch (ph) {
-      case 0: {   // stage the tile's samples (zeros beyond the last valid frame)
-        const float* src = ldg(d.wave + b) + (int64_t)f0 * kHop;
-        const int count = (nvalid - 1) * kHop + kFrame;
-        for (int i = tid; i < kTileSamples; i += kThreads) raw[i] = (i < count) ? src[i] : 0.f;
+      case 0: {   // cooperative staging (the CUDA driver replaces it by a TMA bulk copy when it can)
+        for (int i = tid; i < it.count; i += kThreads) raw[i] = it.src[i];
       } break;
       case 1: {   // pre-emphasis in T into the padded layout + 16-sample partial sums
-        for (int i = tid; i < kTileSamples; i += kThreads) {
-          const T x = (T)raw[i];
-          const T xm = (i > 0) ? (T)raw[i - 1] : T(0);
-          dbuf[phys_idx(i)] = x - T(0.97) * xm;
+        if (it.count == kTileSamples) {          // full tile: no bounds checks
+          for (int i = tid; i < kTileSamples; i += kThreads) {
+            const T x = (T)raw[i];
+            const T xm = (i > 0) ? (T)raw[i - 1] : T(0);
+            dbuf[phys_idx(i)] = x - T(0.97) * xm;
+          }
+        } else {
+          for (int i = tid; i < kTileSamples; i += kThreads) {
+            const T x = (i < it.count) ? (T)raw[i] : T(0);
+            const T xm = (i > 0 && i - 1 < it.count) ? (T)raw[i - 1] : T(0);
+            dbuf[phys_idx(i)] = x - T(0.97) * xm;
+          }
         }
         if (tid < kGroups16) {
-          float s = 0.f;
+          double s = 0.0;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) s += raw[tid * 16 + j];
+          for (int j = 0; j < 16; ++j) {
+            const int i = tid * 16 + ((j + tid) & 15);          // rotated start: 2-way instead of 16-way conflicts
+            s += (i < it.count) ? (double)raw[i] : 0.0;
+          }
           sum16[tid] = s;
         }
       } break;
       case 2: {   // DC removal + window + stage 1 of the real FFT
-        float s = 0.f;
+        double s = 0.0;
 #pragma unroll
         for (int g = 0; g < 25; ++g) s += sum16[10 * f + g];
-        const T c = (T(1) - T(0.97)) * ((T)s / T(kFrame));
+        const T c = (T(1) - T(0.97)) * (T)(s / (double)kFrame);
         T r[25];
 #pragma unroll
         for (int n1 = 0; n1 < 25; ++n1) {
@@ -118,27 +160,28 @@ template <typename T> struct FbankKernel {
       case 3:
         rfft512_stage2<T>(role, f, ex, sP);
         break;
-      case 4: {   // sparse triangular mel + floor + log; role w owns filters w, w+16, ..
-#pragma unroll 1
+      case 4:     // triangular mel, interval form, generated straight-line code (afe_mel_gen.h)
+        mel_intervals_kaldi(role, f, sP, sU, sD);
+        break;
+      case 5: {   // filter m = U[m] + D[m+1]; floor; log
+#pragma unroll
         for (int m = role; m < kMel; m += kRoles) {
-          const int k0 = ldg(mel_start + m), cnt = ldg(mel_count + m), off = ldg(mel_offset + m);
-          float acc = 0.f;
-          for (int i = 0; i < cnt; ++i) acc = fma_f(ldg(mel_w + off + i), sP[(k0 + i) * kTileFrames + f], acc);
+          const float acc = sU[m * kTileFrames + f] + sD[(m + 1) * kTileFrames + f];
           sOut[f * kOutStride + m] = (acc <= kMelFloor) ? log_floor : fast_log(acc);
         }
       } break;
-      case 5: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
+      case 6: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
         if (tid < kMel) {
           double s = 0.0, ss = 0.0;
-          for (int j = 0; j < nvalid; ++j) {
+          for (int j = 0; j < it.nvalid; ++j) {
             const double v = (double)sOut[j * kOutStride + tid];
             s += v; ss += v * v;
           }
-          partials[(item * kMel + tid) * 2] = s;
-          partials[(item * kMel + tid) * 2 + 1] = ss;
+          partials[(it.item * kMel + tid) * 2] = s;
+          partials[(it.item * kMel + tid) * 2 + 1] = ss;
         }
-        float* dst = out + (ldg(d.out_row + b) + f0) * kMel;
-        for (int i = tid; i < nvalid * kMel; i += kThreads) dst[i] = sOut[(i / kMel) * kOutStride + (i % kMel)];
+        float* dst = out + (it.out_row + it.f0) * kMel;
+        for (int i = tid; i < it.nvalid * kMel; i += kThreads) dst[i] = sOut[(i / kMel) * kOutStride + (i % kMel)];
       } break;
     }
   }
@@ -153,8 +196,10 @@ struct FbankStatsKernel {
   BatchDesc d;
   const double* partials;
   float* stats;            // [B][80][2] = (mean, denominator sqrt(var + 1e-7))
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return d.B; }
-  AFE_HD void phase(int, long item, unsigned char*, int tid) const {
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    const long item = it.item;
     if (tid >= kMel) return;
     const long t0 = ldg(d.tile_prefix + item), t1 = ldg(d.tile_prefix + item + 1);
     const int T_b = ldg(d.frames + item);
@@ -181,8 +226,10 @@ struct FbankNormKernel {
   const float* stats;
   float padding_value;
   long items_per_utt;      // ceil(max Tp * 80 / 2048)
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return items_per_utt * d.B; }
-  AFE_HD void phase(int, long item, unsigned char*, int tid) const {
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    const long item = it.item;
     const int b = (int)(item / items_per_utt);
     const long chunk = item % items_per_utt;
     const int T_b = ldg(d.frames + b);

@@ -3,7 +3,8 @@
 // The kernels are written as "phased block programs": a kernel object exposes
 //     static constexpr int kThreads, kPhases;
 //     long  num_items() const;                                   // tiles of work
-//     void  phase(int ph, long item, unsigned char* smem, int tid) const;
+//     Item  prepare(long item) const;                            // per-item context, computed once
+//     void  phase(int ph, const Item&, unsigned char* smem, int tid) const;
 // with the rule that NO per-thread state crosses a phase boundary and, inside a phase, a
 // shared-memory word written by one thread is not touched by any other thread.
 //
@@ -91,6 +92,13 @@ AFE_HD const float* ldg(const float* const* p) {
 #endif
 }
 
+// kernels without per-item context
+struct PlainItem { long item; int buf; int bulk; };
+#define AFE_PLAIN_ITEM                                   \
+  using Item = ::afe::PlainItem;                         \
+  static constexpr bool kAsyncStage = false;             \
+  AFE_HD Item prepare(long item) const { return Item{item, 0, 0}; }
+
 template <typename T> AFE_HD T tmin(T a, T b) { return a < b ? a : b; }
 template <typename T> AFE_HD T tmax(T a, T b) { return a > b ? a : b; }
 
@@ -112,15 +120,101 @@ void  note_error(const char* what, const char* detail);   // records the thread'
 #if AFE_CUDA
 // ------------------------------------------------------------------ CUDA driver
 namespace afe {
+
+// ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier helpers --------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "AFE_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra AFE_DONE;\n\t"
+      "bra AFE_WAIT;\n\t"
+      "AFE_DONE:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+// Kernels with kAsyncStage provide
+//   bool stage_src(const Item&, const float*& src, int& nfloats)   true -> the item's staging
+//        (phase 0) is one contiguous 16-byte-aligned copy of nfloats (multiple of 4) floats
+//   kStageOff / kStageBytes: two staging buffers back to back at kStageOff; Item::buf picks one.
+// The driver prefetches item i+1 with ONE TMA bulk copy while item i computes; items whose
+// staging is not a plain copy (edges, unaligned pointers) run phase 0 cooperatively.
 template <class K>
 __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(const K k) {
   extern __shared__ __align__(16) unsigned char afe_smem[];
   const long n = k.num_items();
-  for (long item = blockIdx.x; item < n; item += gridDim.x) {
-#pragma unroll
-    for (int ph = 0; ph < K::kPhases; ++ph) {
-      k.phase(ph, item, afe_smem, (int)threadIdx.x);
+  const int tid = (int)threadIdx.x;
+  if constexpr (K::kAsyncStage) {
+    // thread 0 prepares item i+1 (tile lookup), publishes it through shared memory and
+    // issues its TMA copy while everybody computes item i.
+    __shared__ __align__(8) uint64_t bars[2];
+    __shared__ typename K::Item items[2];
+    long item = blockIdx.x;
+    if (tid == 0) {
+      mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_mbar_init();
+      if (item < n) {
+        typename K::Item c0 = k.prepare(item);
+        c0.buf = 0;
+        const float* src; int nf;
+        c0.bulk = k.stage_src(c0, src, nf) ? 1 : 0;
+        items[0] = c0;
+        if (c0.bulk) {
+          mbar_expect_tx(&bars[0], (uint32_t)nf * 4u);
+          bulk_g2s(afe_smem + K::kStageOff, src, (uint32_t)nf * 4u, &bars[0]);
+        }
+      }
+    }
+    __syncthreads();
+    uint32_t par[2] = {0u, 0u};
+    for (int it = 0; item < n; item += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const typename K::Item cur = items[buf];
+      const long next = item + gridDim.x;
+      if (tid == 0 && next < n) {
+        typename K::Item nx = k.prepare(next);
+        nx.buf = buf ^ 1;
+        const float* src; int nf;
+        nx.bulk = k.stage_src(nx, src, nf) ? 1 : 0;
+        items[buf ^ 1] = nx;
+        if (nx.bulk) {
+          fence_proxy_async();            // earlier generic-proxy reads of that buffer are done (barriers)
+          mbar_expect_tx(&bars[buf ^ 1], (uint32_t)nf * 4u);
+          bulk_g2s(afe_smem + K::kStageOff + (size_t)(buf ^ 1) * K::kStageBytes, src, (uint32_t)nf * 4u, &bars[buf ^ 1]);
+        }
+      }
+      if (cur.bulk) { mbar_wait(&bars[buf], par[buf]); par[buf] ^= 1u; }
+      else k.phase(0, cur, afe_smem, tid);
       __syncthreads();
+#pragma unroll
+      for (int ph = 1; ph < K::kPhases; ++ph) {
+        k.phase(ph, cur, afe_smem, tid);
+        __syncthreads();
+      }
+    }
+  } else {
+    for (long item = blockIdx.x; item < n; item += gridDim.x) {
+      const typename K::Item ic = k.prepare(item);
+#pragma unroll
+      for (int ph = 0; ph < K::kPhases; ++ph) {
+        k.phase(ph, ic, afe_smem, tid);
+        __syncthreads();
+      }
     }
   }
 }
@@ -151,10 +245,16 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
   std::vector<double> backing((smem_bytes + 64) / sizeof(double) + 2);   // 8-byte aligned, zeroed
   unsigned char* smem = reinterpret_cast<unsigned char*>(backing.data());
   long grid = n < (long)max_blocks ? n : (long)max_blocks;
-  for (long block = 0; block < grid; ++block)
-    for (long item = block; item < n; item += grid)
+  for (long block = 0; block < grid; ++block) {
+    int it = 0;
+    for (long item = block; item < n; item += grid, ++it) {
+      typename K::Item ic = k.prepare(item);
+      ic.buf = K::kAsyncStage ? (it & 1) : 0;          // exercise both staging buffers
+      ic.bulk = 0;
       for (int ph = 0; ph < K::kPhases; ++ph)
-        for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, item, smem, tid);
+        for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
+    }
+  }
   return 0;
 }
 }  // namespace afe

@@ -12,8 +12,10 @@ struct MixKernel {
   static constexpr int kPhases = 1;
   static constexpr int kItem = 4096;
   const float* in; float* mixed; int64_t L;
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return (long)((L + kItem - 1) / kItem); }
-  AFE_HD void phase(int, long item, unsigned char*, int tid) const {
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    const long item = it.item;
     for (int v = tid; v < kItem; v += kThreads) {
       const int64_t i = item * kItem + v;
       if (i < L) mixed[i] = (in[i] + in[L + i]) * 0.5f;

@@ -30,9 +30,11 @@ template <bool STEREO> struct Upsample2xKernel {
   long items_per_row;     // ceil(L / 1024)
   float h[2][15];
 
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return items_per_row * (STEREO ? 1 : rows); }
 
-  AFE_HD void phase(int ph, long item, unsigned char* smem, int tid) const {
+  AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
+    const long item = it.item;
     float* xs = reinterpret_cast<float*>(smem);
     const int row0 = STEREO ? 0 : (int)(item / items_per_row);
     const int64_t n0 = (item % items_per_row) * kPos;
@@ -99,9 +101,11 @@ struct PolyphaseKernel {
 
   AFE_HD int xs_len() const { return (kPeriods - 1) * O + K; }
   AFE_HD size_t smem_bytes() const { return sizeof(float) * ((size_t)xs_len() + 32 * (size_t)K); }
+  AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return (long)rows * jgroups * ntiles; }
 
-  AFE_HD void phase(int ph, long item, unsigned char* smem, int tid) const {
+  AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
+    const long item = it.item;
     float* xs = reinterpret_cast<float*>(smem);
     float* ts = xs + xs_len();
     const long tile = item % ntiles;

@@ -214,6 +214,9 @@ int afe_create(int device, afe_ctx** out) {
     SparseBank mel = make_kaldi_mel_bank();
     ok = ok && (c->d_mel_start = c->upload(mel.start)) && (c->d_mel_count = c->upload(mel.count)) &&
          (c->d_mel_offset = c->upload(mel.offset)) && (c->d_mel_w = c->upload(mel.w));
+    ok = ok && (c->kaldi_mel_dev.up = c->upload(mel.up)) && (c->kaldi_mel_dev.dn = c->upload(mel.dn)) &&
+         (c->kaldi_mel_dev.iv_start = c->upload(mel.iv_start)) && (c->kaldi_mel_dev.iv_count = c->upload(mel.iv_count)) &&
+         (c->kaldi_mel_dev.role_iv = c->upload(mel.role_iv));
     std::vector<double> hn = make_hann_periodic();
     std::vector<float> hn32(hn.size());
     for (size_t i = 0; i < hn.size(); ++i) hn32[i] = (float)(hn[i] * 0.5);
@@ -221,6 +224,9 @@ int afe_create(int device, afe_ctx** out) {
     SparseBank htk = make_htk_mel_bank();
     ok = ok && (c->d_htk_start = c->upload(htk.start)) && (c->d_htk_count = c->upload(htk.count)) &&
          (c->d_htk_offset = c->upload(htk.offset)) && (c->d_htk_w = c->upload(htk.w));
+    ok = ok && (c->htk_mel_dev.up = c->upload(htk.up)) && (c->htk_mel_dev.dn = c->upload(htk.dn)) &&
+         (c->htk_mel_dev.iv_start = c->upload(htk.iv_start)) && (c->htk_mel_dev.iv_count = c->upload(htk.iv_count)) &&
+         (c->htk_mel_dev.role_iv = c->upload(htk.role_iv));
     ok = ok && (c->d_dct = c->upload(make_dct_matrix()));
     c->log_floor = (float)std::log((double)kMelFloor);
   }

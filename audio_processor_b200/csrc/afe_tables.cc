@@ -63,6 +63,37 @@ static void sparsify(const std::vector<double>& dense, int bins, int filters, Sp
   }
 }
 
+// interval form from the edge points `pts` (F+2, ascending) and the bin coordinates `x`
+static void intervalise(const std::vector<double>& pts, const std::vector<double>& x, SparseBank& b) {
+  const int F = b.filters, bins = (int)x.size();
+  b.up.assign(bins, 0.f); b.dn.assign(bins, 0.f);
+  b.iv_start.assign(F + 1, 0); b.iv_count.assign(F + 1, 0);
+  std::vector<int> iv(bins, 0);
+  for (int k = 0; k < bins; ++k) {
+    int i = 0;
+    while (i < F && x[k] >= pts[i + 1]) ++i;          // pts[i] <= x < pts[i+1]  (clamped to 0..F)
+    iv[k] = i;
+    if (i < F) b.up[k] = (float)b.dense[(size_t)k * F + i];
+    if (i >= 1) b.dn[k] = (float)b.dense[(size_t)k * F + i - 1];
+  }
+  for (int i = 0, k = 0; i <= F; ++i) {                 // x ascending -> intervals are contiguous bin runs
+    b.iv_start[i] = k;
+    while (k < bins && iv[k] == i) ++k;
+    b.iv_count[i] = k - b.iv_start[i];
+  }
+  // 16 contiguous interval ranges with balanced cost (1 unit per bin + 1 per interval)
+  b.role_iv.assign(17, F + 1);
+  b.role_iv[0] = 0;
+  const double total = bins + (F + 1);
+  double acc = 0.0;
+  int r = 1;
+  for (int i = 0; i <= F && r < 16; ++i) {
+    acc += b.iv_count[i] + 1;
+    if (acc >= total * r / 16.0) b.role_iv[r++] = i + 1;
+  }
+  for (; r < 16; ++r) b.role_iv[r] = F + 1;
+}
+
 SparseBank make_kaldi_mel_bank() {
   auto mel = [](double f) { return 1127.0 * std::log(1.0 + f / 700.0); };
   const int F = kMel;
@@ -81,7 +112,11 @@ SparseBank make_kaldi_mel_bank() {
       dense[(size_t)k * F + m] = std::max(0.0, std::min(up, down));
     }
   }
-  SparseBank b; sparsify(dense, kBins, F, b); return b;
+  SparseBank b; sparsify(dense, kBins, F, b);
+  std::vector<double> x(kBins);
+  for (int k = 0; k < kBins; ++k) x[k] = mel(bin_hz * k);
+  intervalise(pts, x, b);
+  return b;
 }
 
 SparseBank make_htk_mel_bank() {
@@ -102,7 +137,11 @@ SparseBank make_htk_mel_bank() {
       dense[(size_t)k * F + m] = std::max(0.0, std::min(down, up));
     }
   }
-  SparseBank b; sparsify(dense, kBins, F, b); return b;
+  SparseBank b; sparsify(dense, kBins, F, b);
+  std::vector<double> x(kBins);
+  for (int k = 0; k < kBins; ++k) x[k] = 8000.0 * (double)k / (double)(kBins - 1);
+  intervalise(fp, x, b);
+  return b;
 }
 
 std::vector<double> make_povey_window() {

@@ -36,6 +36,12 @@ struct SparseBank {
   std::vector<int32_t> start, count, offset;
   std::vector<float> w;
   std::vector<double> dense;      // [bins][filters] float64 (tests)
+  // interval form: the F+2 edge points cut the axis into F+1 intervals; a bin in interval i
+  // feeds the UP slope of filter i (i < F) and the DOWN slope of filter i-1 (i >= 1), so
+  //   filter m = U[m] + D[m+1],  U[i] = sum_{k in i} up[k] P[k],  D[i] = sum_{k in i} dn[k] P[k].
+  std::vector<float> up, dn;              // [bins]
+  std::vector<int32_t> iv_start, iv_count;   // [F+1] bins of interval i (contiguous, may be empty)
+  std::vector<int32_t> role_iv;           // [17] intervals [role_iv[r], role_iv[r+1]) of role r, balanced by bins
 };
 SparseBank make_kaldi_mel_bank();        // 80 filters, 20..8000 Hz, mel-space triangles
 SparseBank make_htk_mel_bank();          // 128 filters, 0..8000 Hz, Hz-space triangles (float32 like torchaudio)
