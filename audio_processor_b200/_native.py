@@ -60,11 +60,18 @@ SIGNATURES = {
     "afe_resample_taps": (C.c_int, [C.c_int, C.c_int, c_f32p, C.c_size_t, c_intp, c_intp, c_intp, c_intp]),
     "afe_resample": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_int,
                                C.c_void_p, C.c_void_p, C.c_int64]),
+    "afe_resample_batch_workspace_bytes": (C.c_size_t, [C.c_int]),
+    "afe_resample_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int, C.c_int,
+                                     C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_size_t]),
     "afe_mix_stereo": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "afe_fbank_layout": (C.c_int, [c_i64p, C.c_int, C.c_int, c_i64p, c_i64p]),
     "afe_fbank_workspace_bytes": (C.c_size_t, [c_i64p, C.c_int]),
     "afe_fbank_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
                                   C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "afe_fbank_batch_placed": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, c_i64p, c_i64p,
+                                         C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "afe_acoustic_batch_placed": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
+                                            c_i32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "afe_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "afe_profile_reset": (C.c_int, [C.c_void_p]),
     "afe_profile_read": (C.c_int, [C.c_void_p, c_f64p, c_i64p]),

@@ -14,7 +14,7 @@ struct AcLayout {
   int B = 0;
   long ntiles = 0;
   int64_t rows = 0;
-  size_t off_wave = 0, off_len = 0, off_f1 = 0, off_f2 = 0, off_tprefix = 0, off_rprefix = 0, desc_bytes = 0;
+  size_t off_wave = 0, off_len = 0, off_f1 = 0, off_f2 = 0, off_tprefix = 0, off_rprefix = 0, off_oidx = 0, desc_bytes = 0;
   size_t off_meldb = 0, off_tile = 0, off_mfcc = 0, off_bound = 0, off_gmax = 0, total = 0;
 };
 
@@ -36,6 +36,7 @@ AcLayout ac_layout(const int64_t* lengths, int B) {
   l.off_rprefix = o; o = align_up(o + sizeof(int64_t) * ((size_t)B + 1), 16);
   l.off_f1 = o;      o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
   l.off_f2 = o;      o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
+  l.off_oidx = o;    o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
   l.desc_bytes = o;
   l.off_tile = align_up(o, 256);
   l.off_mfcc = align_up(l.off_tile + sizeof(double) * kTileRec * (size_t)l.ntiles, 256);
@@ -57,6 +58,13 @@ size_t afe_acoustic_workspace_bytes(const int64_t* h_lengths, int batch) {
 
 int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
                        int sample_rate, float* d_out, int32_t* d_status, void* d_workspace, size_t workspace_bytes) {
+  return afe_acoustic_batch_placed(ctx, stream, h_waves, h_lengths, batch, sample_rate, nullptr, d_out, d_status,
+                                   d_workspace, workspace_bytes);
+}
+
+int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                              int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
+                              int32_t* d_status, void* d_workspace, size_t workspace_bytes) {
   if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_acoustic_batch: bad arguments");
   if (batch == 0) return AFE_OK;
   if (sample_rate != 16000)
@@ -76,6 +84,7 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
   int64_t* hrp = reinterpret_cast<int64_t*>(h + l.off_rprefix);
   int32_t* h1 = reinterpret_cast<int32_t*>(h + l.off_f1);
   int32_t* h2 = reinterpret_cast<int32_t*>(h + l.off_f2);
+  int32_t* hoi = reinterpret_cast<int32_t*>(h + l.off_oidx);
   int64_t tiles = 0, rows = 0;
   bool bad = false;
   for (int b = 0; b < batch; ++b) {
@@ -83,11 +92,13 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
     if (F2 > 0 && !h_waves[b]) bad = true;
     hw[b] = h_waves[b]; hl[b] = h_lengths[b]; h1[b] = (int32_t)F1; h2[b] = (int32_t)F2;
     htp[b] = tiles; hrp[b] = rows;
+    hoi[b] = h_out_index ? h_out_index[b] : b;
+    if (hoi[b] < 0) bad = true;
     tiles += (F2 + kTileFrames - 1) / kTileFrames;
     rows += F2;
   }
   htp[batch] = tiles; hrp[batch] = rows;
-  if (bad) { ctx->staging_submit(blk, s); return fail(AFE_ERR_INVALID, "afe_acoustic_batch: NULL waveform"); }
+  if (bad) { ctx->staging_submit(blk, s); return fail(AFE_ERR_INVALID, "afe_acoustic_batch: NULL waveform or negative output row"); }
   unsigned char* ws = static_cast<unsigned char*>(d_workspace);
   const int up = dev_upload_async(ws, h, l.desc_bytes, s);
   ctx->staging_submit(blk, s);
@@ -100,6 +111,7 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
   d.frames2 = reinterpret_cast<const int32_t*>(ws + l.off_f2);
   d.tile_prefix = reinterpret_cast<const int64_t*>(ws + l.off_tprefix);
   d.row_prefix = reinterpret_cast<const int64_t*>(ws + l.off_rprefix);
+  d.out_index = reinterpret_cast<const int32_t*>(ws + l.off_oidx);
   d.B = batch; d.ntiles = l.ntiles;
   double* tile_rec = reinterpret_cast<double*>(ws + l.off_tile);
   double* mfcc_rec = reinterpret_cast<double*>(ws + l.off_mfcc);

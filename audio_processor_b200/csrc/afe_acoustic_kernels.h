@@ -27,6 +27,7 @@ struct AcDesc {
   const int32_t* frames2;     // [B] STFT frames    F2 = 1 + L/160         (0 if L < 400)
   const int64_t* tile_prefix; // [B+1] prefix of ceil(F2/32)
   const int64_t* row_prefix;  // [B+1] prefix of F2 (rows of the mel-dB workspace)
+  const int32_t* out_index;   // [B] output row of waveform b (nullptr: b)
   int B;
   long ntiles;
 };
@@ -359,15 +360,16 @@ struct AcousticFinalKernel {
   AFE_HD long num_items() const { return d.B; }
   AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
     const long item = it.item;
-    float* o = out + item * kAcFeat;
+    const long orow = d.out_index ? (long)ldg(d.out_index + item) : item;
+    float* o = out + orow * kAcFeat;
     const int F1 = ldg(d.frames1 + item), F2 = ldg(d.frames2 + item);
     if (F2 <= 0) {                                   // 'Audio too short'
-      if (tid == 0) status[item] = 1;
+      if (tid == 0) status[orow] = 1;
       for (int i = tid; i < kAcFeat; i += kThreads) o[i] = 0.f;
       return;
     }
     const long t0 = ldg(d.tile_prefix + item), t1 = ldg(d.tile_prefix + item + 1);
-    if (tid == 0) status[item] = 0;
+    if (tid == 0) status[orow] = 0;
     if (tid < 5) {              // rms, zcr over F1 frames; centroid, bandwidth, rolloff over F2
       double s = 0.0, ss = 0.0, mn = 3.0e38, mx = -3.0e38;
       for (long t = t0; t < t1; ++t) {

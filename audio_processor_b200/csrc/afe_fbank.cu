@@ -1,5 +1,7 @@
 // afe_fbank.cu -- C ABI entry point of the batched fbank featuriser.
 #include <algorithm>
+#include <string>
+#include <vector>
 
 #include "afe_ctx.h"
 #include "afe_fbank_kernels.h"
@@ -74,19 +76,17 @@ int afe_fbank_layout(const int64_t* h_lengths, int batch, int group_size, int64_
   return AFE_OK;
 }
 
-int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
-                    int group_size, float padding_value, int precision, int flags, float* d_features,
-                    int32_t* d_mask, void* d_workspace, size_t workspace_bytes) {
-  if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch: bad arguments");
-  if (batch == 0) return AFE_OK;
-  if (!h_waves || !h_lengths || !d_workspace) return fail(AFE_ERR_INVALID, "afe_fbank_batch: NULL argument");
-  if (precision != AFE_PRECISION_F64 && precision != AFE_PRECISION_F32)
-    return fail(AFE_ERR_INVALID, "afe_fbank_batch: unknown precision");
+}  // extern "C"
+
+namespace {
+// shared body: utterance b lands at frame row rows_of[b] of d_features, padded to tp_of[b] frames
+int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
+              const int64_t* rows_of, const int64_t* tp_of, float padding_value, int precision, int flags,
+              float* d_features, int32_t* d_mask, void* d_workspace, size_t workspace_bytes, const char* who) {
   const bool raw_only = (flags & AFE_FBANK_RAW) != 0;
   const FbankLayout l = fbank_layout(h_lengths, batch);
-  if (workspace_bytes < l.total) return fail(AFE_ERR_WORKSPACE, "afe_fbank_batch: workspace too small");
+  if (workspace_bytes < l.total) return fail(AFE_ERR_WORKSPACE, std::string(who) + ": workspace too small");
   cudaStream_t s = (cudaStream_t)stream;
-  const int G = group_size > 0 ? group_size : batch;
 
   // descriptors: pinned staging -> head of the workspace
   StagingBlock* blk = ctx->staging_acquire(l.desc_bytes);
@@ -100,22 +100,20 @@ int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, con
   int32_t* ht = reinterpret_cast<int32_t*>(h + l.off_tp);
   int64_t acc = 0, rows = 0, tp_max = 0;
   bool bad = false;
-  for (int g0 = 0; g0 < batch; g0 += G) {
-    const int n = std::min(G, batch - g0);
-    const int64_t tp = afe_fbank_padded_frames(h_lengths + g0, n);
+  for (int b = 0; b < batch; ++b) {
+    const int64_t T = afe_fbank_num_frames(h_lengths[b]);
+    const int64_t tp = tp_of[b];
+    if (T > 0 && !h_waves[b]) bad = true;
+    if (tp < T || (tp & 1) || rows_of[b] < 0 || (rows_of[b] & 1)) bad = true;
     tp_max = std::max(tp_max, tp);
-    for (int b = g0; b < g0 + n; ++b) {
-      const int64_t T = afe_fbank_num_frames(h_lengths[b]);
-      if (T > 0 && !h_waves[b]) bad = true;
-      hw[b] = h_waves[b]; hl[b] = h_lengths[b]; hf[b] = (int32_t)T; hp[b] = acc; hr[b] = rows; ht[b] = (int32_t)tp;
-      acc += (T + kTileFrames - 1) / kTileFrames;
-      rows += tp;
-    }
+    hw[b] = h_waves[b]; hl[b] = h_lengths[b]; hf[b] = (int32_t)T; hp[b] = acc; hr[b] = rows_of[b]; ht[b] = (int32_t)tp;
+    acc += (T + kTileFrames - 1) / kTileFrames;
+    rows += tp;
   }
   hp[batch] = acc;
   if (bad || (rows > 0 && (!d_features || (!raw_only && !d_mask)))) {
     ctx->staging_submit(blk, s);
-    return fail(AFE_ERR_INVALID, "afe_fbank_batch: NULL waveform or output");
+    return fail(AFE_ERR_INVALID, std::string(who) + ": NULL waveform / output or inconsistent placement");
   }
   unsigned char* ws = static_cast<unsigned char*>(d_workspace);
   const int up = dev_upload_async(ws, h, l.desc_bytes, s);
@@ -148,8 +146,45 @@ int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, con
       rc = afe_launch(nk, 0, ctx->num_sms * 8, s);
     }
   }
-  if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_fbank_batch: launch failed: ") + dev_last_error_string());
+  if (rc != 0) return fail(AFE_ERR_CUDA, std::string(who) + ": launch failed: " + dev_last_error_string());
   return AFE_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
+                    int group_size, float padding_value, int precision, int flags, float* d_features,
+                    int32_t* d_mask, void* d_workspace, size_t workspace_bytes) {
+  if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch: bad arguments");
+  if (batch == 0) return AFE_OK;
+  if (!h_waves || !h_lengths || !d_workspace) return fail(AFE_ERR_INVALID, "afe_fbank_batch: NULL argument");
+  if (precision != AFE_PRECISION_F64 && precision != AFE_PRECISION_F32)
+    return fail(AFE_ERR_INVALID, "afe_fbank_batch: unknown precision");
+  const int G = group_size > 0 ? group_size : batch;
+  std::vector<int64_t> rows_of((size_t)batch), tp_of((size_t)batch);
+  int64_t rows = 0;
+  for (int g0 = 0; g0 < batch; g0 += G) {
+    const int n = std::min(G, batch - g0);
+    const int64_t tp = afe_fbank_padded_frames(h_lengths + g0, n);
+    for (int b = g0; b < g0 + n; ++b) { rows_of[(size_t)b] = rows; tp_of[(size_t)b] = tp; rows += tp; }
+  }
+  return fbank_run(ctx, stream, h_waves, h_lengths, batch, rows_of.data(), tp_of.data(), padding_value, precision,
+                   flags, d_features, d_mask, d_workspace, workspace_bytes, "afe_fbank_batch");
+}
+
+int afe_fbank_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                           int batch, const int64_t* h_out_rows, const int64_t* h_padded_frames,
+                           float padding_value, int precision, int flags, float* d_features, int32_t* d_mask,
+                           void* d_workspace, size_t workspace_bytes) {
+  if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch_placed: bad arguments");
+  if (batch == 0) return AFE_OK;
+  if (!h_waves || !h_lengths || !h_out_rows || !h_padded_frames || !d_workspace)
+    return fail(AFE_ERR_INVALID, "afe_fbank_batch_placed: NULL argument");
+  if (precision != AFE_PRECISION_F64 && precision != AFE_PRECISION_F32)
+    return fail(AFE_ERR_INVALID, "afe_fbank_batch_placed: unknown precision");
+  return fbank_run(ctx, stream, h_waves, h_lengths, batch, h_out_rows, h_padded_frames, padding_value, precision,
+                   flags, d_features, d_mask, d_workspace, workspace_bytes, "afe_fbank_batch_placed");
 }
 
 }  // extern "C"

@@ -30,6 +30,8 @@
 #define AFE_HD inline
 #define AFE_RESTRICT __restrict__
 typedef void* cudaStream_t;
+struct alignas(8) float2 { float x, y; };
+struct alignas(16) float4 { float x, y, z, w; };
 #endif
 
 namespace afe {

@@ -24,6 +24,24 @@ struct MixKernel {
 };
 }  // namespace afe
 
+namespace {
+// one launch of the 1:2 kernel over `ncalls` calls (device descriptors) or the inline call
+int launch_up2x(afe_ctx* ctx, cudaStream_t s, const ResampleTaps& t, const UpCall* d_calls, const UpCall& one,
+                int ncalls, int rows, bool stereo_mix, long nitems = -1) {
+  if (nitems < 0) nitems = (long)((one.L + 1023) / 1024) * (stereo_mix ? 1 : rows);
+  if (stereo_mix) {
+    Upsample2xKernel<true> k;
+    k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = 2; k.nitems = nitems;
+    for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
+    return afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * 8, s);
+  }
+  Upsample2xKernel<false> k;
+  k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = rows; k.nitems = nitems;
+  for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
+  return afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * 8, s);
+}
+}  // namespace
+
 extern "C" {
 
 int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed) {
@@ -51,18 +69,8 @@ int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_
   {
   ProfScope ps(ctx, AFE_K_RESAMPLE, s);
   if (t.O == 1 && t.N == 2 && t.K == 15) {
-    const long ipr = (long)((length + 1023) / 1024);
-    if (rows == 2 && d_mixed) {
-      Upsample2xKernel<true> k;
-      k.in = d_in; k.out = d_out; k.mixed = d_mixed; k.L = length; k.rows = 2; k.items_per_row = ipr;
-      for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
-      rc = afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * 8, s);
-    } else {
-      Upsample2xKernel<false> k;
-      k.in = d_in; k.out = d_out; k.mixed = nullptr; k.L = length; k.rows = rows; k.items_per_row = ipr;
-      for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
-      rc = afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * 8, s);
-    }
+    UpCall one{d_in, d_out, d_mixed, length, 0};
+    rc = launch_up2x(ctx, s, t, nullptr, one, 1, rows, d_mixed != nullptr);
   } else {
     PolyphaseKernel k;
     k.in = d_in; k.out = d_out; k.tapsT = dt->d_tapsT; k.L = length; k.out_len = out_length;
@@ -84,6 +92,58 @@ int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_
     }
   }
   if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_resample: launch failed: ") + dev_last_error_string());
+  return AFE_OK;
+}
+
+size_t afe_resample_batch_workspace_bytes(int ncalls) {
+  return (sizeof(UpCall) * (size_t)(ncalls > 0 ? ncalls : 1) + 255) / 256 * 256;
+}
+
+int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, const int64_t* h_lengths, int ncalls,
+                       int rows, int orig_hz, int new_hz, float* const* h_out, float* const* h_mixed,
+                       void* d_workspace, size_t workspace_bytes) {
+  if (!ctx || ncalls < 0 || rows <= 0 || orig_hz <= 0 || new_hz <= 0)
+    return fail(AFE_ERR_INVALID, "afe_resample_batch: bad arguments");
+  if (ncalls == 0) return AFE_OK;
+  if (!h_in || !h_lengths || !h_out) return fail(AFE_ERR_INVALID, "afe_resample_batch: NULL argument");
+  if (orig_hz == new_hz) return fail(AFE_ERR_INVALID, "afe_resample_batch: equal rates need no resampling");
+  if (h_mixed && rows != 2) return fail(AFE_ERR_INVALID, "afe_resample_batch: mixed output needs exactly 2 rows");
+  const DeviceTaps* dt = ctx->get_taps(orig_hz, new_hz);
+  if (!dt) return AFE_ERR_CUDA;
+  const ResampleTaps& t = dt->host;
+  if (!(t.O == 1 && t.N == 2 && t.K == 15) || ncalls == 1) {
+    // other rate pairs: one launch per call through the generic path
+    for (int c = 0; c < ncalls; ++c) {
+      const int rc = afe_resample(ctx, stream, h_in[c], rows, h_lengths[c], orig_hz, new_hz, h_out[c],
+                                  h_mixed ? h_mixed[c] : nullptr, resampled_length(h_lengths[c], orig_hz, new_hz));
+      if (rc != AFE_OK) return rc;
+    }
+    return AFE_OK;
+  }
+  const size_t need = afe_resample_batch_workspace_bytes(ncalls);
+  if (!d_workspace || workspace_bytes < need) return fail(AFE_ERR_WORKSPACE, "afe_resample_batch: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  StagingBlock* blk = ctx->staging_acquire(need);
+  if (!blk) return AFE_ERR_CUDA;
+  UpCall* hc = static_cast<UpCall*>(blk->host);
+  const bool mix = h_mixed != nullptr;
+  long items = 0;
+  bool bad = false;
+  for (int c = 0; c < ncalls; ++c) {
+    if (h_lengths[c] < 0 || (h_lengths[c] > 0 && (!h_in[c] || !h_out[c] || (mix && !h_mixed[c])))) bad = true;
+    hc[c] = UpCall{h_in[c], h_out[c], mix ? h_mixed[c] : nullptr, h_lengths[c], (int64_t)items};
+    items += (long)((h_lengths[c] + 1023) / 1024) * (mix ? 1 : rows);
+  }
+  if (bad) { ctx->staging_submit(blk, s); return fail(AFE_ERR_INVALID, "afe_resample_batch: NULL buffer or negative length"); }
+  const int up = dev_upload_async(d_workspace, hc, sizeof(UpCall) * (size_t)ncalls, s);
+  ctx->staging_submit(blk, s);
+  if (up != 0) return AFE_ERR_CUDA;
+  int rc;
+  {
+    ProfScope ps(ctx, AFE_K_RESAMPLE, s);
+    rc = launch_up2x(ctx, s, t, static_cast<const UpCall*>(d_workspace), UpCall{}, ncalls, rows, mix, items);
+  }
+  if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_resample_batch: launch failed: ") + dev_last_error_string());
   return AFE_OK;
 }
 

@@ -11,73 +11,138 @@
 namespace afe {
 
 // ------------------------------------------------------------------ 1:2 upsampler (8 k -> 16 k)
-// O = 1, N = 2, K = 15 (width 7).  One item = 1024 input positions of one row group;
-// 256 threads x 4 positions.  STEREO: both rows + mixed = (a + c) * 0.5 in one pass.
+// O = 1, N = 2, K = 15 (width 7).  One item = 1024 input positions of one call (STEREO: both
+// rows + mixed = (a + c) * 0.5 in the same pass; mono: one row).  256 threads; thread t owns
+// the position pairs q = t and t + 256; a pair yields 4 consecutive outputs, so a warp's
+// store is one contiguous 512-byte run of 128-bit words (coalesced), and the tile is staged
+// with 128-bit loads.  A launch covers a whole batch of calls.
+struct UpCall {               // one call of a batched launch (device array, or inline for one call)
+  const float* in;            // [rows][L]
+  float* out;                 // [rows][2L]
+  float* mixed;               // [2L] or nullptr
+  int64_t L;
+  int64_t item0;              // first item of this call in the launch
+};
+
 template <bool STEREO> struct Upsample2xKernel {
   static constexpr int kThreads = 256;
   static constexpr int kMinBlocks = 4;
   static constexpr int kPhases = 2;
   static constexpr int kPos = 1024;                 // input positions per item
-  static constexpr int kTile = kPos + 16;           // staged samples per row: [n0-8, n0+1032)
+  static constexpr int kTile = kPos + 16;           // staged samples per row: x[n0-8 .. n0+1032)
   static constexpr int kRows = STEREO ? 2 : 1;
   static constexpr size_t kSmemBytes = sizeof(float) * kTile * kRows;
+  static constexpr bool kAsyncStage = false;
 
-  const float* in;        // [rows][L]
-  float* out;             // [rows][2L]
-  float* mixed;           // [2L] (STEREO only)
-  int64_t L;
-  int rows;               // total rows (STEREO: 2)
-  long items_per_row;     // ceil(L / 1024)
+  const UpCall* calls;    // device array [ncalls] (nullptr: `one`)
+  UpCall one;
+  int ncalls;
+  int rows;               // rows per call (STEREO: 2)
+  long nitems;
   float h[2][15];
 
-  AFE_PLAIN_ITEM
-  AFE_HD long num_items() const { return items_per_row * (STEREO ? 1 : rows); }
+  struct Item { long item; int buf; int bulk; const float* src; float* dst; float* mix; int64_t L; int64_t n0; };
+
+  AFE_HD long num_items() const { return nitems; }
+
+  AFE_HD Item prepare(long item) const {
+    Item it;
+    it.item = item; it.buf = 0; it.bulk = 0;
+    UpCall c;
+    if (calls == nullptr) {
+      c = one;
+    } else {
+      int lo = 0, hi = ncalls;                       // calls[lo].item0 <= item < calls[hi].item0
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (ldg(&calls[mid].item0) <= item) lo = mid; else hi = mid;
+      }
+      c.in = ldg(&calls[lo].in); c.out = const_cast<float*>(ldg(const_cast<const float* const*>(&calls[lo].out)));
+      c.mixed = const_cast<float*>(ldg(const_cast<const float* const*>(&calls[lo].mixed)));
+      c.L = ldg(&calls[lo].L); c.item0 = ldg(&calls[lo].item0);
+    }
+    const long local = item - (long)c.item0;
+    const long ipr = (long)((c.L + kPos - 1) / kPos);
+    const int row0 = STEREO ? 0 : (int)(local / ipr);
+    it.n0 = (int64_t)(local % ipr) * kPos;
+    it.L = c.L;
+    it.src = c.in + (int64_t)row0 * c.L;
+    it.dst = c.out + (int64_t)row0 * 2 * c.L;
+    it.mix = c.mixed;
+    return it;
+  }
 
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
-    const long item = it.item;
     float* xs = reinterpret_cast<float*>(smem);
-    const int row0 = STEREO ? 0 : (int)(item / items_per_row);
-    const int64_t n0 = (item % items_per_row) * kPos;
+    const int64_t n0 = it.n0, L = it.L;
     if (ph == 0) {
+#pragma unroll
       for (int r = 0; r < kRows; ++r) {
-        const float* src = in + (int64_t)(row0 + r) * L;
-        for (int i = tid; i < kTile; i += kThreads) {
-          const int64_t g = n0 - 8 + i;
-          xs[r * kTile + i] = (g >= 0 && g < L) ? src[g] : 0.f;
+        const float* src = it.src + (int64_t)r * L;
+        const float* p0 = src + (n0 - 8);
+        if (n0 >= 8 && n0 - 8 + kTile <= L && (reinterpret_cast<uintptr_t>(p0) & 15u) == 0) {
+          const float4* s4 = reinterpret_cast<const float4*>(p0);
+          float4* d4 = reinterpret_cast<float4*>(xs + r * kTile);
+          for (int i = tid; i < kTile / 4; i += kThreads) d4[i] = s4[i];
+        } else {
+          for (int i = tid; i < kTile; i += kThreads) {
+            const int64_t g = n0 - 8 + i;
+            xs[r * kTile + i] = (g >= 0 && g < L) ? src[g] : 0.f;
+          }
         }
       }
       return;
     }
-    // ph == 1: positions n0 + 4*tid .. +3; xp[n + k] = x[n + k - 7] = xs[(n - n0) + k + 1]
-    float y[kRows][8];
+    // ph == 1: pair q = tid + 256 j covers positions n0 + 2q, n0 + 2q + 1 -> outputs 4q .. 4q+3 of
+    // the item.  xp[n + k] = x[n + k - 7] = xs[(n - n0) + k + 1]; the window xs[2q .. 2q+17]
+    // is read as nine 64-bit words.
+    const bool vec_out = ((reinterpret_cast<uintptr_t>(it.dst) & 15u) == 0) && ((L & 1) == 0 || !STEREO) &&
+                         (!STEREO || (reinterpret_cast<uintptr_t>(it.mix) & 15u) == 0);
 #pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-      float x[20];
+    for (int j = 0; j < kPos / 2 / kThreads; ++j) {
+      const int q = tid + kThreads * j;
+      const int64_t n = n0 + 2 * q;
+      if (n >= L) break;
+      float y[kRows][4];
 #pragma unroll
-      for (int i = 0; i < 20; ++i) x[i] = xs[r * kTile + 4 * tid + i];
+      for (int r = 0; r < kRows; ++r) {
+        float w[18];
+        const float2* w2 = reinterpret_cast<const float2*>(xs + r * kTile + 2 * q);
 #pragma unroll
-      for (int p = 0; p < 4; ++p)
+        for (int i = 0; i < 9; ++i) { const float2 v = w2[i]; w[2 * i] = v.x; w[2 * i + 1] = v.y; }
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          float acc = 0.f;
+        for (int p = 0; p < 2; ++p)
 #pragma unroll
-          for (int k = 0; k < 15; ++k) acc = fma_f(h[j][k], x[p + k + 1], acc);
-          y[r][2 * p + j] = acc;
+          for (int ph2 = 0; ph2 < 2; ++ph2) {
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < 15; ++k) acc = fma_f(h[ph2][k], w[p + k + 1], acc);
+            y[r][2 * p + ph2] = acc;
+          }
+      }
+      const bool full = (n + 1 < L);
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) {
+        float* dst = it.dst + (int64_t)r * 2 * L + 2 * n;
+        if (full && vec_out) {
+          *reinterpret_cast<float4*>(dst) = float4{y[r][0], y[r][1], y[r][2], y[r][3]};
+        } else {
+          dst[0] = y[r][0]; dst[1] = y[r][1];
+          if (full) { dst[2] = y[r][2]; dst[3] = y[r][3]; }
         }
-    }
-    const int64_t n = n0 + 4 * tid;
-    if (n >= L) return;
-    const int nout = (int)tmin<int64_t>(8, 2 * (L - n));
+      }
+      if (STEREO) {
+        float* dst = it.mix + 2 * n;
+        float m[4];
 #pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-      float* dst = out + (int64_t)(row0 + r) * 2 * L + 2 * n;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) if (i < nout) dst[i] = y[r][i];
-    }
-    if (STEREO) {
-      float* dst = mixed + 2 * n;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) if (i < nout) dst[i] = (y[0][i] + y[kRows - 1][i]) * 0.5f;
+        for (int i = 0; i < 4; ++i) m[i] = (y[0][i] + y[kRows - 1][i]) * 0.5f;
+        if (full && vec_out) {
+          *reinterpret_cast<float4*>(dst) = float4{m[0], m[1], m[2], m[3]};
+        } else {
+          dst[0] = m[0]; dst[1] = m[1];
+          if (full) { dst[2] = m[2]; dst[3] = m[3]; }
+        }
+      }
     }
   }
 };

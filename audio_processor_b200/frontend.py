@@ -44,44 +44,126 @@ class CallFrontend:
         self.precision = precision
         self.acoustic = acoustic
         self._tables = {}
+        self._copy_stream = None
 
-    def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True
-                      ) -> FrontendResult:
-        """``calls``: (C, L) float32 tensors (host -- ideally pinned -- or device)."""
-        fe, sr_t = self.fe, self.target_sample_rate
+    def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True,
+                      sub_batch: Optional[int] = None) -> FrontendResult:
+        """``calls``: (C, L) float32 tensors (host -- ideally pinned -- or device).
+
+        Every integer of the result (chunk table, length-sorted order, the padded length of
+        each batch of ``batch_size`` chunks, the output row of every chunk) depends on the call
+        lengths only, so the whole output layout is planned on the host first.  The calls are
+        then processed in sub-batches of ``sub_batch`` calls: while sub-batch k is resampled,
+        featurised (all three streams in one launch, each chunk written to its final rows)
+        and its acoustic rows computed, sub-batch k+1 is uploaded on a second stream."""
+        fe, sr_t, dev = self.fe, self.target_sample_rate, self.device
         res = FrontendResult(n_calls=len(calls))
         chunk_samples = int(self.chunk_duration_sec * sr_t)
         step = chunk_samples - int(self.overlap_sec * sr_t)
-        mixed_p, agent_p, client_p, lens = [], [], [], []
+        # ---- plan (host, integers only)
+        louts, first_chunk, lens = [], [], []
         for ci, call in enumerate(calls):
-            res.call_seconds += call.shape[1] / float(sample_rate)
-            x = call.to(self.device, non_blocking=True)
-            if sample_rate != sr_t:
-                if x.shape[0] == 2:
-                    y, mixed = fe.resample(x, sample_rate, sr_t, want_mixed=True)
-                else:
-                    y = fe.resample(x, sample_rate, sr_t); mixed = y
-            else:
-                y = x.contiguous(); mixed = fe.mix_stereo(y) if y.shape[0] == 2 else y
-            res.waveforms.append((y, mixed))
-            Lr = int(y.shape[1])
-            pa = y.data_ptr()
-            pc = pa + 4 * Lr if y.shape[0] == 2 else pa
-            pm = mixed.data_ptr()
+            L = int(call.shape[1])
+            res.call_seconds += L / float(sample_rate)
+            Lr = fe.resampled_length(L, sample_rate, sr_t) if sample_rate != sr_t else L
+            louts.append(Lr)
+            first_chunk.append(len(res.chunks))
             for idx, (s, e) in enumerate(self._chunk_table(Lr, chunk_samples, step)):
-                res.chunks.append((ci, idx, s, e))
-                mixed_p.append(pm + 4 * s); agent_p.append(pa + 4 * s); client_p.append(pc + 4 * s); lens.append(e - s)
+                res.chunks.append((ci, idx, s, e)); lens.append(e - s)
+        first_chunk.append(len(res.chunks))
         n = len(res.chunks)
         if n == 0:
             return res
-        # transcribe_batch: stable sort by mixed length, slices of batch_size
-        res.order = sorted(range(n), key=lens.__getitem__)
+        G = self.batch_size
+        res.order = sorted(range(n), key=lens.__getitem__)       # transcribe_batch: stable sort by length
         slens = [lens[i] for i in res.order]
-        for key, lst in (("stereo", mixed_p), ("agent", agent_p), ("client", client_p)):
-            res.features[key] = fe.fbank_ptrs([lst[i] for i in res.order], slens, padding_value=self.padding_value,
-                                              precision=self.precision, group_size=self.batch_size)
+        tps, total_rows = fe.fbank_layout(slens, G)
+        row_of, tp_of, pos = [0] * n, [0] * n, 0
+        for g, tp in enumerate(tps):
+            for j in range(g * G, min(n, (g + 1) * G)):
+                row_of[res.order[j]] = pos; tp_of[res.order[j]] = tp; pos += tp
+        half = total_rows // 2
+        feat_all = torch.empty((3 * half, 160), dtype=torch.float32, device=dev)
+        mask_all = torch.empty((3 * half,), dtype=torch.int32, device=dev)
         if self.acoustic:
-            rows, status = fe.acoustic_ptrs(agent_p + client_p, lens + lens, sr_t)
+            rows = torch.empty((2 * n, 38), dtype=torch.float32, device=dev)
+            status = torch.empty((2 * n,), dtype=torch.int32, device=dev)
+        # ---- pipeline over sub-batches of calls
+        any_host = any(not c.is_cuda for c in calls)
+        sb = int(sub_batch) if sub_batch else (8 if any_host else len(calls))
+        main = torch.cuda.current_stream(dev)
+        if any_host and self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+        uploads = []                                              # (device tensors, ready event) per sub-batch
+
+        def upload(k0):
+            sub = calls[k0:k0 + sb]
+            if not any_host:
+                return [c.to(dev) for c in sub], None
+            with torch.cuda.stream(self._copy_stream):
+                xs = [c.to(dev, non_blocking=True) for c in sub]
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            return xs, ev
+
+        starts = list(range(0, len(calls), sb))
+        pending = upload(starts[0])
+        res.waveforms = [None] * len(calls)                       # type: ignore[list-item]
+        for si, k0 in enumerate(starts):
+            xs, ev = pending
+            if si + 1 < len(starts):
+                pending = upload(starts[si + 1])                  # enqueue the next upload before this compute
+            if ev is not None:
+                main.wait_event(ev)
+                for x in xs:
+                    if x.is_cuda:
+                        x.record_stream(main)
+            # resample / mix: stereo and mono calls of the sub-batch, one launch each
+            for want_rows in (2, 1):
+                ids = [k0 + j for j, x in enumerate(xs) if int(x.shape[0]) == want_rows]
+                if not ids:
+                    continue
+                grp = [xs[i - k0] for i in ids]
+                if sample_rate != sr_t:
+                    if want_rows == 2:
+                        ys, ms = fe.resample_batch(grp, sample_rate, sr_t, want_mixed=True)
+                    else:
+                        ys = fe.resample_batch(grp, sample_rate, sr_t); ms = ys
+                else:
+                    ys = [x.contiguous() for x in grp]
+                    ms = [fe.mix_stereo(y) for y in ys] if want_rows == 2 else ys
+                for i, y, m in zip(ids, ys, ms):
+                    res.waveforms[i] = (y, m)
+            bad = [k0 + j for j, x in enumerate(xs) if int(x.shape[0]) not in (1, 2)]
+            if bad:
+                raise ValueError(f"process_calls: call {bad[0]} has {int(xs[bad[0] - k0].shape[0])} channels")
+            c0, c1 = first_chunk[k0], first_chunk[min(k0 + sb, len(calls))]
+            if c1 == c0:
+                continue
+            mixed_p, agent_p, client_p = [], [], []
+            for ci, _, s, _ in res.chunks[c0:c1]:
+                y, m = res.waveforms[ci]
+                Lr = int(y.shape[1])
+                pa = y.data_ptr()
+                pc = pa + 4 * Lr if y.shape[0] == 2 else pa
+                mixed_p.append(m.data_ptr() + 4 * s); agent_p.append(pa + 4 * s); client_p.append(pc + 4 * s)
+            sub_lens = lens[c0:c1]
+            sub_rows = row_of[c0:c1]
+            fe.fbank_placed(mixed_p + agent_p + client_p, sub_lens * 3,
+                            sub_rows + [r + total_rows for r in sub_rows] + [r + 2 * total_rows for r in sub_rows],
+                            tp_of[c0:c1] * 3, feat_all, mask_all, padding_value=self.padding_value,
+                            precision=self.precision)
+            if self.acoustic:
+                fe.acoustic_ptrs(agent_p + client_p, sub_lens * 2, sr_t, out=rows, status=status,
+                                 out_index=list(range(c0, c1)) + list(range(n + c0, n + c1)))
+        for si, key in enumerate(("stereo", "agent", "client")):
+            views, r = [], si * half
+            for g, tp in enumerate(tps):
+                ng, h = min(G, n - g * G), tp // 2
+                views.append((feat_all[r:r + ng * h].view(ng, h, 160), mask_all[r:r + ng * h].view(ng, h)))
+                r += ng * h
+            res.features[key] = views
+        if self.acoustic:
             if acoustic_to_host:
                 rows = rows.cpu(); status = status.cpu()
             res.acoustic_rows, res.acoustic_status = rows, status

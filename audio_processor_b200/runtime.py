@@ -64,6 +64,13 @@ class Frontend:
             self._tls.ws2 = ws
         return ws
 
+    def _workspace3(self, nbytes: int) -> torch.Tensor:
+        ws = getattr(self._tls, "ws3", None)        # resample batch descriptors
+        if ws is None or ws.numel() < nbytes:
+            ws = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8, device=self.device)
+            self._tls.ws3 = ws
+        return ws
+
     def _to_device_1d(self, waves: Sequence[Wave]) -> Tuple[List[torch.Tensor], List[int]]:
         """Mono float32 device views of every waveform; host inputs share ONE pinned staging
         buffer and ONE H2D copy (offsets rounded to 4 floats so rows stay 16-byte aligned)."""
@@ -119,6 +126,43 @@ class Frontend:
         out = out.reshape(tuple(lead) + (Lo,))
         return (out, mixed) if want_mixed else out
 
+    def resample_batch(self, calls: Sequence[torch.Tensor], orig: int, new: int, want_mixed: bool = False):
+        """``Resample(orig, new)`` over a batch of (rows, L_c) float32 CUDA tensors in ONE launch
+        (the per-file loop of ``AudioProcessor.process_batch``).  Returns a list of outputs (and a
+        list of (1, L') mixed tensors with ``want_mixed``); all outputs are views of one
+        allocation, every view 16-byte aligned."""
+        n = len(calls)
+        if n == 0:
+            return ([], []) if want_mixed else []
+        xs = [c.to(device=self.device, dtype=torch.float32).contiguous() for c in calls]
+        rows = int(xs[0].shape[0])
+        if any(x.dim() != 2 or int(x.shape[0]) != rows for x in xs):
+            raise ValueError("resample_batch: every call must be (rows, L) with the same number of rows")
+        lens = [int(x.shape[1]) for x in xs]
+        louts = [self.resampled_length(L, orig, new) for L in lens]
+        per = rows + (1 if want_mixed else 0)
+        offs, total = [], 0
+        for lo in louts:
+            offs.append(total)
+            total += per * ((lo + 3) // 4 * 4)
+        buf = torch.empty((max(total, 1),), dtype=torch.float32, device=self.device)
+        outs, mixes, p_out, p_mix = [], [], [], []
+        for o, lo in zip(offs, louts):
+            pad = (lo + 3) // 4 * 4                 # the block is padded, rows stay contiguous
+            y = buf[o:o + rows * lo].view(rows, lo)
+            outs.append(y); p_out.append(y.data_ptr())
+            if want_mixed:
+                m = buf[o + rows * pad:o + rows * pad + lo].view(1, lo)
+                mixes.append(m); p_mix.append(m.data_ptr())
+        ws = self._workspace3(int(self.lib.afe_resample_batch_workspace_bytes(n)))
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_resample_batch(
+                self.ctx, self._stream(), _native.ptr_array([x.data_ptr() for x in xs]), _native.i64_array(lens), n,
+                rows, int(orig), int(new), _native.ptr_array(p_out), _native.ptr_array(p_mix) if want_mixed else None,
+                C.c_void_p(ws.data_ptr()), ws.numel()))
+        self._tls.keep_rs = xs                      # inputs stay alive until the next call on this thread
+        return (outs, mixes) if want_mixed else outs
+
     def mix_stereo(self, x: torch.Tensor) -> torch.Tensor:
         x = x.to(device=self.device, dtype=torch.float32).contiguous()
         L = int(x.shape[-1])
@@ -172,6 +216,33 @@ class Frontend:
             r += n * h
         return out if G else out[0]
 
+    def fbank_layout(self, lens: Sequence[int], group_size: int = 0):
+        """(padded frames per group, total frame rows) of the grouped output (afe_fbank_layout)."""
+        B = len(lens)
+        G = int(group_size) if group_size and group_size > 0 else 0
+        ng = ((B + G - 1) // G if G else 1) if B else 0
+        tps = (C.c_int64 * max(ng, 1))()
+        rows = C.c_int64()
+        self.lib.check(self.lib.afe_fbank_layout(_native.i64_array(lens), B, G, tps, C.byref(rows)))
+        return [int(tps[g]) for g in range(ng)], int(rows.value)
+
+    def fbank_placed(self, ptrs: Sequence[int], lens: Sequence[int], out_rows: Sequence[int],
+                     padded_frames: Sequence[int], feat: torch.Tensor, mask: torch.Tensor,
+                     padding_value: float = 0.0, precision: int = _native.PRECISION_F64) -> None:
+        """Featurise device waveforms into caller-placed rows of ``feat`` (rows/2, 160) and
+        ``mask`` (rows/2,): utterance b starts at frame row ``out_rows[b]`` and is padded to
+        ``padded_frames[b]`` frames (afe_fbank_batch_placed)."""
+        B = len(ptrs)
+        if B == 0:
+            return
+        lens_c = _native.i64_array(lens)
+        ws = self._workspace(int(self.lib.afe_fbank_workspace_bytes(lens_c, B)))
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_fbank_batch_placed(
+                self.ctx, self._stream(), _native.ptr_array(ptrs), lens_c, B, _native.i64_array(out_rows),
+                _native.i64_array(padded_frames), float(padding_value), int(precision), 0,
+                C.c_void_p(feat.data_ptr()), C.c_void_p(mask.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel()))
+
     # ------------------------------------------------------------------ acoustic
     def acoustic(self, waves: Sequence[Wave], sample_rate: int = 16000) -> Tuple[torch.Tensor, torch.Tensor]:
         """((B, 38) float32 feature rows, (B,) int32 status) on the device; see afe.h."""
@@ -180,17 +251,23 @@ class Frontend:
         self._tls.keep = dev_waves
         return out
 
-    def acoustic_ptrs(self, ptrs: Sequence[int], lens: Sequence[int], sample_rate: int = 16000):
+    def acoustic_ptrs(self, ptrs: Sequence[int], lens: Sequence[int], sample_rate: int = 16000,
+                      out: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
+                      out_index: Optional[Sequence[int]] = None):
+        """With ``out`` / ``status`` / ``out_index`` waveform b is written to row ``out_index[b]``
+        of the caller's (N, 38) / (N,) tensors (afe_acoustic_batch_placed)."""
         B = len(ptrs)
-        out = torch.empty((B, 38), dtype=torch.float32, device=self.device)
-        status = torch.empty((B,), dtype=torch.int32, device=self.device)
+        if out is None:
+            out = torch.empty((B, 38), dtype=torch.float32, device=self.device)
+            status = torch.empty((B,), dtype=torch.int32, device=self.device)
         if B == 0:
             return out, status
         lens_c = _native.i64_array(lens)
+        idx_c = (C.c_int32 * B)(*[int(i) for i in out_index]) if out_index is not None else None
         ws = self._workspace2(int(self.lib.afe_acoustic_workspace_bytes(lens_c, B)))
         with torch.cuda.device(self.device):
-            self.lib.check(self.lib.afe_acoustic_batch(
-                self.ctx, self._stream(), _native.ptr_array(ptrs), lens_c, B, int(sample_rate),
+            self.lib.check(self.lib.afe_acoustic_batch_placed(
+                self.ctx, self._stream(), _native.ptr_array(ptrs), lens_c, B, int(sample_rate), idx_c,
                 C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel()))
         return out, status
 

@@ -219,7 +219,8 @@ def run_afe(a):
         e2e_value = total_hours / (ms_e2e / 1e3)
         fb_ms, fb_n = prof["fbank"]
         peak, peak_src = measured_peak()
-        frames_per_launch = frames_per_stream            # one launch per stream
+        # the three streams' frames of a step, spread over however many launches the step used
+        frames_per_launch = 3.0 * frames_per_stream * a.steps / max(fb_n, 1)
         achieved = frames_per_launch * FBANK_BYTES_PER_FRAME / (fb_ms / max(fb_n, 1) * 1e-3) / 1e9 if fb_ms > 0 else None
         traffic_pf = ncu_traffic()
         kernel_ms = {k: round(v[0] / a.steps, 4) for k, v in prof.items() if v[1]}

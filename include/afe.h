@@ -81,6 +81,16 @@ int afe_resample_taps(int orig_hz, int new_hz, float* h_taps, size_t cap_floats,
 int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_t length,
                  int orig_hz, int new_hz, float* d_out, float* d_mixed, int64_t out_length);
 
+/* The same for a batch of calls in ONE launch (AudioProcessor.process_batch iterates
+ * split_audio over the files of a batch, services/audio_processor.py:324-347).  h_in[c] /
+ * h_out[c] / h_mixed[c] are DEVICE pointers of call c ([rows, h_lengths[c]] in,
+ * [rows, ceil(new*L/orig)] out); h_mixed may be NULL.  d_workspace holds the per-call
+ * descriptors (afe_resample_batch_workspace_bytes). */
+size_t afe_resample_batch_workspace_bytes(int ncalls);
+int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, const int64_t* h_lengths,
+                       int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                       float* const* h_mixed, void* d_workspace, size_t workspace_bytes);
+
 /* mixed = (row0 + row1) * 0.5 for waveforms that need no resampling (split_audio :123-131) */
 int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed);
 
@@ -103,6 +113,17 @@ int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, con
                     int batch, int group_size, float padding_value, int precision, int flags,
                     float* d_features, int32_t* d_mask, void* d_workspace, size_t workspace_bytes);
 
+/* afe_fbank_batch with explicit placement: utterance b is written at frame row
+ * h_out_rows[b] (even) of d_features / mask row h_out_rows[b]/2 and padded to
+ * h_padded_frames[b] frames (even, >= its own frame count).  Lets a caller featurise the
+ * members of the reference's length-sorted batches in any order and in several launches
+ * (e.g. per file, overlapped with the upload of the next file) into ONE output laid out as
+ * afe_fbank_layout describes.  Workspace: afe_fbank_workspace_bytes(h_lengths, batch). */
+int afe_fbank_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                           int batch, const int64_t* h_out_rows, const int64_t* h_padded_frames,
+                           float padding_value, int precision, int flags, float* d_features, int32_t* d_mask,
+                           void* d_workspace, size_t workspace_bytes);
+
 /* AcousticSentimentAnalyzer._extract_acoustic_features for a batch of mono 16 kHz
  * waveforms (services/sentiment_analysis.py:807-894).  d_out is (batch, 38) float32 in
  * the reference's key order, with slot 11 ("tempo") holding the spectral-flux energy
@@ -112,6 +133,11 @@ size_t afe_acoustic_workspace_bytes(const int64_t* h_lengths, int batch);
 int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
                        int batch, int sample_rate, float* d_out, int32_t* d_status,
                        void* d_workspace, size_t workspace_bytes);
+
+/* the same, writing waveform b to row h_out_index[b] of d_out / d_status (NULL: row b) */
+int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                              int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
+                              int32_t* d_status, void* d_workspace, size_t workspace_bytes);
 
 /* ---- per-kernel device timing (CUDA events on the caller's stream) --------------------
  * While enabled every kernel launch of this context is bracketed by cudaEvents.

@@ -46,6 +46,28 @@ def test_emu_resample_ragged_lengths(L):
     assert np.array_equal(mixed[0], (ref[0] + ref[1]) * np.float32(0.5))
 
 
+def test_emu_resample_batch_matches_per_call():
+    rng = np.random.default_rng(11)
+    lens = [1, 2, 5, 1023, 1024, 1026, 2500, 4097, 0, 3001]
+    calls = [rng.uniform(-0.5, 0.5, (2, L)).astype(np.float32) for L in lens]
+    outs, mixes = emu_util.resample_batch(calls, 8000, 16000, want_mixed=True)
+    for c, o, m in zip(calls, outs, mixes):
+        ref = np_resample.resample(c, 8000, 16000) if c.shape[1] else np.zeros((2, 0), np.float32)
+        assert np.array_equal(o, ref)
+        assert np.array_equal(m[0], (ref[0] + ref[1]) * np.float32(0.5))
+    outs = emu_util.resample_batch(calls, 8000, 16000)          # no mixed output: rows are separate items
+    for c, o in zip(calls, outs):
+        if c.shape[1]:
+            assert np.array_equal(o, np_resample.resample(c, 8000, 16000))
+    mono = [c[:1] for c in calls if c.shape[1]]
+    for c, o in zip(mono, emu_util.resample_batch(mono, 8000, 16000)):
+        assert np.array_equal(o, np_resample.resample(c, 8000, 16000))
+    x = rng.uniform(-0.5, 0.5, (1, 3000)).astype(np.float32)    # other rate pairs loop over the generic kernel
+    pair = [x, x[:, :1777]]
+    for c, o in zip(pair, emu_util.resample_batch(pair, 16000, 8000)):
+        assert np.array_equal(o, np_resample.resample(c, 16000, 8000))
+
+
 def test_emu_resample_generic_rates():
     x = (np.random.default_rng(5).uniform(-0.5, 0.5, (1, 3000))).astype(np.float32)
     for orig, new in ((16000, 8000), (48000, 16000), (22050, 16000)):

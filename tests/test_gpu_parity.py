@@ -243,3 +243,49 @@ def test_call_frontend_whole_path(fe):
     ref_a = np_acoustic.acoustic_features(ref1[1])
     got = np.asarray(list(client_d[2].values())); exp = np.asarray(list(ref_a.values()))
     assert np.all(np.abs(got - exp) <= np.maximum(2e-3, 2e-4 * np.abs(exp)))
+
+
+def test_resample_batch_one_launch(fe):
+    rng = np.random.default_rng(21)
+    lens = [1, 2, 5, 1023, 1024, 1026, 2500, 4097, 0, 100001]
+    calls = [rng.uniform(-0.5, 0.5, (2, L)).astype(np.float32) for L in lens]
+    outs, mixes = fe.resample_batch([_t(c, fe) for c in calls], 8000, 16000, want_mixed=True)
+    for c, o, m in zip(calls, outs, mixes):
+        ref = np_resample.resample(c, 8000, 16000) if c.shape[1] else np.zeros((2, 0), np.float32)
+        assert np.array_equal(o.cpu().numpy(), ref)
+        assert np.array_equal(m.cpu().numpy()[0], (ref[0] + ref[1]) * np.float32(0.5))
+    mono = [c[:1] for c in calls if c.shape[1]]
+    for c, o in zip(mono, fe.resample_batch([_t(c, fe) for c in mono], 8000, 16000)):
+        assert np.array_equal(o.cpu().numpy(), np_resample.resample(c, 8000, 16000))
+
+
+def test_call_frontend_pipelined_equals_single_shot(fe):
+    """Host (pinned) inputs in sub-batches over two streams == device inputs in one shot, and both
+    equal the per-call drop-in path; covers mono calls and sample_rate == target."""
+    import torch
+    from audio_processor_b200 import CallFrontend, synth
+    calls = [synth.make_call(d, 8000, 300 + i, 2) for i, d in enumerate((30.0, 12.5, 51.0, 0.02, 26.0))]
+    calls.append(synth.make_call(27.0, 8000, 399, 1))
+    cf = CallFrontend(fe.device, batch_size=4)
+    a = cf.process_calls([c.pin_memory() for c in calls], 8000, sub_batch=2)
+    b = cf.process_calls([c.to(fe.device) for c in calls], 8000)
+    assert a.chunks == b.chunks and a.order == b.order
+    for key in ("stereo", "agent", "client"):
+        assert len(a.features[key]) == len(b.features[key])
+        for (fa, ma), (fb, mb) in zip(a.features[key], b.features[key]):
+            assert torch.equal(fa, fb) and torch.equal(ma, mb)
+    assert torch.equal(a.acoustic_rows, b.acoustic_rows.cpu()) and torch.equal(a.acoustic_status, b.acoustic_status.cpu())
+    # against the oracle: the sorted batches of the mixed stream
+    refs = [np_resample.resample(c.numpy(), 8000, 16000) for c in calls]
+    mixed = [((r[0] + r[1]) * np.float32(0.5)) if r.shape[0] == 2 else r[0] for r in refs]
+    waves = [mixed[ci][s:e] for ci, _, s, e in a.chunks]
+    for g, (feat, mask) in enumerate(a.features["stereo"]):
+        idx = a.order[g * 4:(g + 1) * 4]
+        ref_f, ref_m = np_fbank.featurise([waves[i] for i in idx])
+        assert np.array_equal(mask.cpu().numpy(), ref_m)
+        _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+    # 16 kHz input: no resampling, mixed = mean of the rows
+    c16 = synth.make_call(3.0, 16000, 5, 2)
+    r16 = cf.process_calls([c16], 16000)
+    ref_f, ref_m = np_fbank.featurise([((c16[0] + c16[1]) * 0.5).numpy()])
+    _cmp_nan(r16.features["stereo"][0][0].cpu().numpy(), ref_f, 1e-3)

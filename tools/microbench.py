@@ -55,6 +55,11 @@ def main():
         med, best = timed(lambda: fe.resample(call, 8000, 16000, want_mixed=True), a.reps, flush)
         byts = 2_400_000 * 2 * 4 + 3 * 4_800_000 * 4
         res["resample_8k_stereo_5min"] = {"ms_med": med, "ms_best": best, "GBps_best": byts / best / 1e6}
+    if not a.only or a.only == "resample":
+        calls16 = [(torch.rand(2, 2_400_000, generator=g) - 0.5).to(dev) for _ in range(16)]
+        med, best = timed(lambda: fe.resample_batch(calls16, 8000, 16000, want_mixed=True), a.reps, flush)
+        res["resample_8k_stereo_5min_x16_one_launch"] = {"ms_med": med, "ms_best": best, "GBps_best": 16 * byts / best / 1e6}
+        del calls16
     # fbank on N full 25 s chunks
     wav = (torch.rand(a.chunks, 400_000, generator=g) - 0.5).to(dev)
     chunks = [wav[i] for i in range(a.chunks)]
