@@ -130,9 +130,10 @@ int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_
     rc = afe_launch(mk, 0, 1 << 20, s);
   }
   if (rc == 0) {
-    AcousticMfccKernel ck{d, meldb, gmax, ctx->d_dct, boundary, mfcc_rec};
+    AcousticMfccKernel ck;
+    ck.d = d; ck.meldb = meldb; ck.gmax = gmax; ck.boundary = boundary; ck.mfcc_rec = mfcc_rec;
     ProfScope ps(ctx, AFE_K_AC_MFCC, s);
-    rc = afe_launch(ck, AcousticMfccKernel::kSmemBytes, ctx->num_sms * 4, s);
+    rc = afe_launch(ck, AcousticMfccKernel::kSmemBytes, ctx->num_sms * 8, s);
   }
   if (rc == 0) {
     AcousticFinalKernel fk{d, tile_rec, mfcc_rec, boundary, d_out, d_status};

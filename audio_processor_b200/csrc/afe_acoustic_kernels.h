@@ -71,7 +71,7 @@ struct AcousticTileKernel {
   static constexpr size_t kStageOff = AcSmem::kRawOff;
   static constexpr size_t kStageBytes = AcSmem::kRawBytes;
 
-  struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int F1; int64_t L; const float* wave; int64_t row0; };
+  struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int F1; int F2; int64_t L; const float* wave; int64_t row0; };
 
   AcDesc d;
   const float* hann;        // [400] periodic Hann / 2
@@ -87,12 +87,30 @@ struct AcousticTileKernel {
     int t;
     ac_locate(d, item, it.b, t);
     it.item = item; it.buf = 0; it.bulk = 0;
-    it.f0 = t * kTileFrames;
-    it.nvalid = tmin(kTileFrames, ldg(d.frames2 + it.b) - it.f0);
-    it.F1 = ldg(d.frames1 + it.b);
-    it.L = ldg(d.len + it.b);
-    it.wave = ldg(d.wave + it.b);
-    it.row0 = ldg(d.row_prefix + it.b);
+    fill(it, it.b, t * kTileFrames);
+    return it;
+  }
+  AFE_HD void fill(Item& it, int b, int f0) const {
+    it.b = b; it.f0 = f0;
+    it.F2 = ldg(d.frames2 + b);
+    it.nvalid = tmin(kTileFrames, it.F2 - f0);
+    it.F1 = ldg(d.frames1 + b);
+    it.L = ldg(d.len + b);
+    it.wave = ldg(d.wave + b);
+    it.row0 = ldg(d.row_prefix + b);
+  }
+  // item cur.item + 1 without a search: next tile of the same waveform, else the next waveform with frames
+  AFE_HD Item next(const Item& cur, long item) const {
+    Item it = cur;
+    it.item = item;
+    if (cur.f0 + kTileFrames < cur.F2) {
+      it.f0 = cur.f0 + kTileFrames;
+      it.nvalid = tmin(kTileFrames, cur.F2 - it.f0);
+      return it;
+    }
+    int b = cur.b + 1;
+    while (b + 1 < d.B && ldg(d.frames2 + b) <= 0) ++b;
+    fill(it, b, 0);
     return it;
   }
   // interior tiles (no reflection) are one contiguous aligned copy
@@ -285,60 +303,99 @@ struct AcousticMaxKernel {
   }
 };
 
+// One item = one 32-frame tile; 4 warps, lane = frame, warp w owns mel bins [32w, 32w+32).
+// The DCT coefficients are immediates of generated straight-line FFMAs (afe_mel_gen.h; sm_100
+// has no constant-bank ALU operands, a table in the parameters costs one LDCU per FFMA): per
+// frame 128 shared loads (as 128-bit words) and 13 x 128 FFMAs, no table loads.
 struct AcousticMfccKernel {
-  static constexpr int kThreads = 512;
-  static constexpr int kMinBlocks = 2;
-  static constexpr int kPhases = 3;
-  static constexpr size_t kSmemBytes = sizeof(float) * (kTileFrames * kDbStride + 16 * 32 + 512);
-  AcDesc d; const float* meldb; const float* gmax; const float* dct; const float* boundary;
+  static constexpr int kThreads = 128;
+  static constexpr int kMinBlocks = 8;
+  static constexpr int kPhases = 4;
+  static constexpr int kRow = kAcMel + 4;           // 132: rows stay 16-byte aligned, LDS.128 by lane = frame is conflict-free
+  static constexpr int kWarps = kThreads / 32;
+  static constexpr size_t kSmemBytes =
+      sizeof(float) * (kTileFrames * kRow + kWarps * kMfcc * 32 + kMfcc * 32 + kThreads);
+  static constexpr bool kAsyncStage = false;
+  AcDesc d; const float* meldb; const float* gmax; const float* boundary;
   double* mfcc_rec;        // [ntiles][14][2]: 13 x (sum, sum sq) + (boundary flux^2, 0)
-  AFE_PLAIN_ITEM
+
+  struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int has_next; float cut; int64_t row0; };
   AFE_HD long num_items() const { return d.ntiles; }
+  AFE_HD Item prepare(long item) const {
+    Item it;
+    int t;
+    ac_locate(d, item, it.b, t);
+    it.item = item; it.buf = 0; it.bulk = 0;
+    it.f0 = t * kTileFrames;
+    it.nvalid = tmin(kTileFrames, ldg(d.frames2 + it.b) - it.f0);
+    it.has_next = (item + 1 < ldg(d.tile_prefix + it.b + 1)) ? 1 : 0;   // another tile of the same waveform follows
+    it.cut = ldg(gmax + it.b) - 80.f;
+    it.row0 = ldg(d.row_prefix + it.b);
+    return it;
+  }
+
+  template <int W> AFE_HD void partial_dct(const float* AFE_RESTRICT sD, float* AFE_RESTRICT sC, int f) const {
+    float acc[kMfcc];
+#pragma unroll
+    for (int c = 0; c < kMfcc; ++c) acc[c] = 0.f;
+    const float4* row = reinterpret_cast<const float4*>(sD + f * kRow + 32 * W);
+    if (W == 0) dct13_partial_0(row, acc);
+    else if (W == 1) dct13_partial_1(row, acc);
+    else if (W == 2) dct13_partial_2(row, acc);
+    else dct13_partial_3(row, acc);
+#pragma unroll
+    for (int c = 0; c < kMfcc; ++c) sC[(W * kMfcc + c) * 32 + f] = acc[c];
+  }
+
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
-    const long item = it.item;
     float* sD = reinterpret_cast<float*>(smem);
-    float* sC = sD + kTileFrames * kDbStride;
-    float* sX = sC + 16 * 32;
-    int b, t;
-    ac_locate(d, item, b, t);
-    const int F2 = ldg(d.frames2 + b);
-    const int f0 = t * kTileFrames;
-    const int nvalid = tmin(kTileFrames, F2 - f0);
-    const bool has_next = (item + 1 < ldg(d.tile_prefix + b + 1));     // another tile of the same waveform follows
-    if (ph == 0) {
-      const float cut = ldg(gmax + b) - 80.f;
-      const float* src = meldb + (ldg(d.row_prefix + b) + f0) * kAcMel;
-      for (int i = tid; i < kTileFrames * kAcMel; i += kThreads)
-        sD[(i >> 7) * kDbStride + (i & 127)] = (i < nvalid * kAcMel) ? tmax(src[i], cut) : 0.f;
+    float* sC = sD + kTileFrames * kRow;         // [4][13][32] partial dot products
+    float* sV = sC + kWarps * kMfcc * 32;        // [13][32] coefficients
+    float* sX = sV + kMfcc * 32;                 // [128] boundary flux partials
+    if (ph == 0) {        // clamp at max - 80 dB while staging the tile (coalesced 128-bit loads)
+      const float4* src = reinterpret_cast<const float4*>(meldb + (it.row0 + it.f0) * kAcMel);
+      const int nq = it.nvalid * (kAcMel / 4);
+      for (int i = tid; i < kTileFrames * (kAcMel / 4); i += kThreads) {
+        float4 v = float4{0.f, 0.f, 0.f, 0.f};
+        if (i < nq) {
+          v = src[i];
+          v.x = tmax(v.x, it.cut); v.y = tmax(v.y, it.cut); v.z = tmax(v.z, it.cut); v.w = tmax(v.w, it.cut);
+        }
+        *reinterpret_cast<float4*>(sD + (i >> 5) * kRow + (i & 31) * 4) = v;
+      }
       // spectral flux across the tile boundary: relu(first frame of tile+1 - last frame of this tile)
       float fl = 0.f;
-      if (has_next && tid < kBins) {
-        const float* last = boundary + item * 2 * kBoundary + kBoundary;
-        const float* first = boundary + (item + 1) * 2 * kBoundary;
-        fl = tmax(first[tid] - last[tid], 0.f);
+      if (it.has_next) {
+        const float* last = boundary + it.item * 2 * kBoundary + kBoundary;
+        const float* first = boundary + (it.item + 1) * 2 * kBoundary;
+        for (int q = tid; q < kBins; q += kThreads) fl += tmax(first[q] - last[q], 0.f);
       }
       sX[tid] = fl;
     } else if (ph == 1) {
-      const int c = tid >> 5, f = tid & 31;
-      if (c < kMfcc) {
-        float acc = 0.f;
-        for (int n = 0; n < kAcMel; ++n) acc = fma_f(sD[f * kDbStride + n], ldg(dct + c * kAcMel + n), acc);
-        sC[c * 32 + f] = acc;
-      } else if (c == 13) {          // 16 partial sums of the boundary flux terms
-        float s = 0.f;
-        for (int q = f; q < kBins; q += 32) s += sX[q];
-        sC[13 * 32 + f] = s;
+      const int f = tid & 31;
+      switch (tid >> 5) {
+        case 0: partial_dct<0>(sD, sC, f); break;
+        case 1: partial_dct<1>(sD, sC, f); break;
+        case 2: partial_dct<2>(sD, sC, f); break;
+        default: partial_dct<3>(sD, sC, f); break;
+      }
+    } else if (ph == 2) {
+      for (int i = tid; i < kMfcc * 32; i += kThreads) {
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) v += sC[w * kMfcc * 32 + i];
+        sV[i] = v;
       }
     } else if (tid < kMfcc) {
       double s = 0.0, ss = 0.0;
-      for (int j = 0; j < nvalid; ++j) { const double v = (double)sC[tid * 32 + j]; s += v; ss += v * v; }
-      mfcc_rec[(item * 14 + tid) * 2] = s;
-      mfcc_rec[(item * 14 + tid) * 2 + 1] = ss;
-    } else if (tid == 13) {
+      for (int j = 0; j < it.nvalid; ++j) { const double v = (double)sV[tid * 32 + j]; s += v; ss += v * v; }
+      mfcc_rec[(it.item * 14 + tid) * 2] = s;
+      mfcc_rec[(it.item * 14 + tid) * 2 + 1] = ss;
+    } else if (tid == 32) {
       float fl = 0.f;
-      for (int j = 0; j < 32; ++j) fl += sC[13 * 32 + j];
-      mfcc_rec[(item * 14 + 13) * 2] = (double)fl * (double)fl;
-      mfcc_rec[(item * 14 + 13) * 2 + 1] = 0.0;
+      for (int j = 0; j < kThreads; ++j) fl += sX[j];
+      mfcc_rec[(it.item * 14 + 13) * 2] = (double)fl * (double)fl;
+      mfcc_rec[(it.item * 14 + 13) * 2 + 1] = 0.0;
     }
   }
 };

@@ -46,6 +46,7 @@ struct afe_ctx {
   int32_t *d_htk_start = nullptr, *d_htk_count = nullptr, *d_htk_offset = nullptr;
   float* d_htk_w = nullptr;
   float* d_dct = nullptr;                                       // [13][128]
+  std::vector<float> h_dct;                                     // host copy: rides in the MFCC kernel's parameters
   float log_floor = 0.f;
   struct MelDev { const float* up; const float* dn; const int32_t* iv_start; const int32_t* iv_count; const int32_t* role_iv; };
   MelDev kaldi_mel_dev{}, htk_mel_dev{};

@@ -46,8 +46,6 @@ int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, dou
               const T* window, const T* tw) {
   FbankKernel<T> k;
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
-  const auto& m = ctx->kaldi_mel_dev;
-  k.mel = MelTables{m.up, m.dn, m.iv_start, m.iv_count, m.role_iv};
   k.log_floor = ctx->log_floor;
   ProfScope ps(ctx, AFE_K_FBANK, s);
   return afe_launch(k, FbankSmem<T>::kBytes, ctx->num_sms, s);

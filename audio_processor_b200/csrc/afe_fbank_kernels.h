@@ -54,16 +54,16 @@ constexpr int kMelIv = kMel + 1;                  // 81 intervals
 template <typename T> struct FbankSmem {
   static constexpr size_t kRawBytes = sizeof(float) * kTileSamples;                 // 21440 per staging buffer
   static constexpr size_t kRawOff = 0;                                              // float[2][5360]
-  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double[336]
-  static constexpr size_t kDOff = kSumOff + sizeof(double) * 336;                   // T[5528] | sP + sOut
+  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double[336] + double c[32]
+  static constexpr size_t kCOff = kSumOff + sizeof(double) * 336;
+  static constexpr size_t kDOff = kCOff + sizeof(double) * 32;                      // T[5528] | sP + sOut
   static constexpr size_t kDBytesT = sizeof(T) * (kTileSamples + kTileSamples / 32 + 8);
   static constexpr size_t kPBytes = sizeof(float) * (kBins * kTileFrames);          // 32896
   static constexpr size_t kOutBytes = sizeof(float) * (kTileFrames * kOutStride);   // 10368
   static constexpr size_t kDBytes = (kDBytesT > kPBytes + kOutBytes ? kDBytesT : kPBytes + kOutBytes);
-  static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*32] | sU,sD
+  static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*32]
   static constexpr size_t kExBytesT = sizeof(cplx<T>) * 16 * 16 * kTileFrames;
-  static constexpr size_t kUDBytes = sizeof(float) * 2 * kMelIv * kTileFrames;      // 20736
-  static constexpr size_t kBytes = kExOff + (kExBytesT > kUDBytes ? kExBytesT : kUDBytes);
+  static constexpr size_t kBytes = kExOff + kExBytesT;
 };
 
 template <typename T> struct FbankKernel {
@@ -74,28 +74,48 @@ template <typename T> struct FbankKernel {
   static constexpr size_t kStageOff = FbankSmem<T>::kRawOff;
   static constexpr size_t kStageBytes = FbankSmem<T>::kRawBytes;
 
-  struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int count; const float* src; int64_t out_row; };
+  struct Item { long item; int buf; int bulk; int b; int f0; int nfr; int nvalid; int count; const float* src; int64_t out_row; };
 
   BatchDesc d;
   float* out;              // [rows][80] raw log-mel lands at its final position
   double* partials;        // [ntiles][80][2]  (sum, sum of squares) per mel bin
   const T* window;         // [400]  povey * 32768 / 2
   const T* tw512;          // [16][16][2]
-  MelTables mel;
   float log_floor;         // float32(log(float64(mel_floor)))
 
   AFE_HD long num_items() const { return d.ntiles; }
 
+  AFE_HD void fill(Item& it, int b, int f0) const {
+    it.b = b; it.f0 = f0;
+    it.nfr = ldg(d.frames + b);
+    it.nvalid = tmin(kTileFrames, it.nfr - f0);
+    it.count = (it.nvalid - 1) * kHop + kFrame;
+    it.src = ldg(d.wave + b) + (int64_t)f0 * kHop;
+    it.out_row = ldg(d.out_row + b);
+  }
   AFE_HD Item prepare(long item) const {
     Item it;
-    int t;
-    locate_tile(d, item, it.b, t);
+    int b, t;
+    locate_tile(d, item, b, t);
     it.item = item; it.buf = 0; it.bulk = 0;
-    it.f0 = t * kTileFrames;
-    it.nvalid = tmin(kTileFrames, ldg(d.frames + it.b) - it.f0);
-    it.count = (it.nvalid - 1) * kHop + kFrame;
-    it.src = ldg(d.wave + it.b) + (int64_t)it.f0 * kHop;
-    it.out_row = ldg(d.out_row + it.b);
+    fill(it, b, t * kTileFrames);
+    return it;
+  }
+  // item cur.item + 1: the next tile of the same utterance, else the first tile of the next
+  // utterance that has frames (no search; utterance data is reloaded only on a crossing)
+  AFE_HD Item next(const Item& cur, long item) const {
+    Item it = cur;
+    it.item = item;
+    if (cur.f0 + kTileFrames < cur.nfr) {
+      it.f0 = cur.f0 + kTileFrames;
+      it.nvalid = tmin(kTileFrames, cur.nfr - it.f0);
+      it.count = (it.nvalid - 1) * kHop + kFrame;
+      it.src = cur.src + (int64_t)kTileFrames * kHop;
+      return it;
+    }
+    int b = cur.b + 1;
+    while (b + 1 < d.B && ldg(d.frames + b) <= 0) ++b;
+    fill(it, b, 0);
     return it;
   }
   // the tile is one contiguous run of `count` samples: a single TMA bulk copy when 16-byte aligned
@@ -108,12 +128,11 @@ template <typename T> struct FbankKernel {
     using S = FbankSmem<T>;
     float* raw = reinterpret_cast<float*>(smem + S::kRawOff + (size_t)it.buf * S::kRawBytes);
     double* sum16 = reinterpret_cast<double*>(smem + S::kSumOff);
+    T* sc = reinterpret_cast<T*>(smem + S::kCOff);
     T* dbuf = reinterpret_cast<T*>(smem + S::kDOff);
     float* sP = reinterpret_cast<float*>(smem + S::kDOff);
     float* sOut = reinterpret_cast<float*>(smem + S::kDOff + S::kPBytes);
     cplx<T>* ex = reinterpret_cast<cplx<T>*>(smem + S::kExOff);
-    float* sU = reinterpret_cast<float*>(smem + S::kExOff);
-    float* sD = sU + kMelIv * kTileFrames;
     const int role = tid >> 5, f = tid & 31;
 
     switch (ph) {
@@ -121,11 +140,19 @@ template <typename T> struct FbankKernel {
         for (int i = tid; i < it.count; i += kThreads) raw[i] = it.src[i];
       } break;
       case 1: {   // pre-emphasis in T into the padded layout + 16-sample partial sums
+        // element i = tid + 512 j sits at i + (i >> 5) = tid + role + 528 j
         if (it.count == kTileSamples) {          // full tile: no bounds checks
-          for (int i = tid; i < kTileSamples; i += kThreads) {
-            const T x = (T)raw[i];
-            const T xm = (i > 0) ? (T)raw[i - 1] : T(0);
-            dbuf[phys_idx(i)] = x - T(0.97) * xm;
+          T* dp = dbuf + tid + role;
+          const float* rp = raw + tid;
+#pragma unroll
+          for (int j = 0; j < kTileSamples / kThreads; ++j) {
+            const T x = (T)rp[kThreads * j];
+            const T xm = (j == 0 && tid == 0) ? T(0) : (T)rp[kThreads * j - 1];
+            dp[(kThreads + 16) * j] = x - T(0.97) * xm;
+          }
+          if (tid < kTileSamples % kThreads) {
+            constexpr int j = kTileSamples / kThreads;
+            dp[(kThreads + 16) * j] = (T)rp[kThreads * j] - T(0.97) * (T)rp[kThreads * j - 1];
           }
         } else {
           for (int i = tid; i < kTileSamples; i += kThreads) {
@@ -135,20 +162,31 @@ template <typename T> struct FbankKernel {
           }
         }
         if (tid < kGroups16) {
-          double s = 0.0;
+          double s0 = 0.0, s1 = 0.0;
+          const float* g = raw + tid * 16;
+          if (tid * 16 + 16 <= it.count) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int i = tid * 16 + ((j + tid) & 15);          // rotated start: 2-way instead of 16-way conflicts
-            s += (i < it.count) ? (double)raw[i] : 0.0;
+            for (int j = 0; j < 16; j += 2) {    // rotated start: 2-way instead of 16-way bank conflicts
+              s0 += (double)g[(j + tid) & 15];
+              s1 += (double)g[(j + 1 + tid) & 15];
+            }
+          } else {
+            for (int j = 0; j < 16; ++j) s0 += (tid * 16 + j < it.count) ? (double)g[j] : 0.0;
           }
-          sum16[tid] = s;
+          sum16[tid] = s0 + s1;
         }
       } break;
-      case 2: {   // DC removal + window + stage 1 of the real FFT
-        double s = 0.0;
+      case 2: {   // DC term of every frame: c = (1 - 0.97) * mean(frame)
+        if (tid < kTileFrames) {
+          double s[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-        for (int g = 0; g < 25; ++g) s += sum16[10 * f + g];
-        const T c = (T(1) - T(0.97)) * (T)(s / (double)kFrame);
+          for (int g = 0; g < 25; ++g) s[g % 5] += sum16[10 * tid + g];
+          const double tot = ((s[0] + s[1]) + (s[2] + s[3])) + s[4];
+          sc[tid] = (T)((1.0 - 0.97) * (tot * (1.0 / (double)kFrame)));
+        }
+      } break;
+      case 3: {   // DC removal + window + stage 1 of the real FFT
+        const T c = sc[f];
         T r[25];
 #pragma unroll
         for (int n1 = 0; n1 < 25; ++n1) {
@@ -157,31 +195,37 @@ template <typename T> struct FbankKernel {
         }
         rfft512_stage1<T>(r, role, f, tw512, ex);
       } break;
-      case 3:
+      case 4:
         rfft512_stage2<T>(role, f, ex, sP);
         break;
-      case 4:     // triangular mel, interval form, generated straight-line code (afe_mel_gen.h)
-        mel_intervals_kaldi(role, f, sP, sU, sD);
-        break;
-      case 5: {   // filter m = U[m] + D[m+1]; floor; log
-#pragma unroll
-        for (int m = role; m < kMel; m += kRoles) {
-          const float acc = sU[m * kTileFrames + f] + sD[(m + 1) * kTileFrames + f];
-          sOut[f * kOutStride + m] = (acc <= kMelFloor) ? log_floor : fast_log(acc);
-        }
+      case 5: {   // triangular mel bank (generated straight-line code) + floor + log
+        float* row = sOut + f * kOutStride;
+        const float lf = log_floor;
+        mel_filters_kaldi(role, f, sP, [row, lf](int m, float acc) {
+          row[m] = (acc <= kMelFloor) ? lf : fast_log(acc);
+        });
       } break;
       case 6: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
         if (tid < kMel) {
-          double s = 0.0, ss = 0.0;
-          for (int j = 0; j < it.nvalid; ++j) {
-            const double v = (double)sOut[j * kOutStride + tid];
-            s += v; ss += v * v;
+          double s[4] = {0.0, 0.0, 0.0, 0.0}, q[4] = {0.0, 0.0, 0.0, 0.0};
+          if (it.nvalid == kTileFrames) {
+#pragma unroll
+            for (int j = 0; j < kTileFrames; ++j) {
+              const double v = (double)sOut[j * kOutStride + tid];
+              s[j & 3] += v; q[j & 3] += v * v;
+            }
+          } else {
+            for (int j = 0; j < it.nvalid; ++j) {
+              const double v = (double)sOut[j * kOutStride + tid];
+              s[0] += v; q[0] += v * v;
+            }
           }
-          partials[(it.item * kMel + tid) * 2] = s;
-          partials[(it.item * kMel + tid) * 2 + 1] = ss;
+          partials[(it.item * kMel + tid) * 2] = (s[0] + s[1]) + (s[2] + s[3]);
+          partials[(it.item * kMel + tid) * 2 + 1] = (q[0] + q[1]) + (q[2] + q[3]);
+        } else if (tid >= 96) {
+          float* dst = out + (it.out_row + it.f0) * kMel;
+          for (int i = tid - 96; i < it.nvalid * kMel; i += kThreads - 96) dst[i] = sOut[(i / kMel) * kOutStride + (i % kMel)];
         }
-        float* dst = out + (it.out_row + it.f0) * kMel;
-        for (int i = tid; i < it.nvalid * kMel; i += kThreads) dst[i] = sOut[(i / kMel) * kOutStride + (i % kMel)];
       } break;
     }
   }
@@ -214,16 +258,18 @@ struct FbankStatsKernel {
 };
 
 // in-place normalisation, right padding and the stride-2 attention mask.
-// One item = 2048 consecutive floats of one utterance's (Tp x 80) plane.
+// One item = 2048 consecutive floats of one utterance's (Tp x 80) plane, moved as 128-bit
+// words (4 mel bins of one frame; planes start 16-byte aligned because rows are 320 bytes).
 struct FbankNormKernel {
   static constexpr int kThreads = 256;
   static constexpr int kMinBlocks = 4;
   static constexpr int kPhases = 1;
   static constexpr int kItemFloats = 2048;
+  static constexpr int kQuadsPerRow = kMel / 4;   // 20
   BatchDesc d;
   float* feat;             // [rows][80]
   int32_t* mask;           // [rows/2]
-  const float* stats;
+  const float* stats;      // [B][80][2] = (mean, denominator)
   float padding_value;
   long items_per_utt;      // ceil(max Tp * 80 / 2048)
   AFE_PLAIN_ITEM
@@ -233,19 +279,26 @@ struct FbankNormKernel {
     const int b = (int)(item / items_per_utt);
     const long chunk = item % items_per_utt;
     const int T_b = ldg(d.frames + b);
-    const int64_t plane = (int64_t)ldg(d.tp + b) * kMel;
+    const int64_t plane4 = (int64_t)ldg(d.tp + b) * kQuadsPerRow;
     const int64_t row0 = ldg(d.out_row + b);
-    float* base = feat + row0 * kMel;
-    for (int v = tid; v < kItemFloats; v += kThreads) {
-      const int64_t idx = chunk * kItemFloats + v;
-      if (idx >= plane) break;
-      const int64_t t = idx / kMel;
-      const int m = (int)(idx % kMel);
-      float y = padding_value;
-      if (t < T_b) y = (base[idx] - ldg(stats + ((int64_t)b * kMel + m) * 2)) / ldg(stats + ((int64_t)b * kMel + m) * 2 + 1);
-      base[idx] = y;
+    float4* base = reinterpret_cast<float4*>(feat + row0 * kMel);
+    const float4* st = reinterpret_cast<const float4*>(stats + (int64_t)b * kMel * 2);
+#pragma unroll
+    for (int v = tid; v < kItemFloats / 4; v += kThreads) {
+      const int64_t i4 = chunk * (kItemFloats / 4) + v;
+      if (i4 >= plane4) break;
+      const int64_t t = i4 / kQuadsPerRow;
+      const int m4 = (int)(i4 - t * kQuadsPerRow);
+      float4 y = float4{padding_value, padding_value, padding_value, padding_value};
+      if (t < T_b) {
+        const float4 x = base[i4];
+        const float4 s0 = ldg(st + 2 * m4), s1 = ldg(st + 2 * m4 + 1);   // (mean, den) x 4 bins
+        y.x = (x.x - s0.x) / s0.y; y.y = (x.y - s0.z) / s0.w;
+        y.z = (x.z - s1.x) / s1.y; y.w = (x.w - s1.z) / s1.w;
+      }
+      base[i4] = y;
       // the stacked mask takes the ODD frame's bit: mask[b][j] = (2j+1 < T_b)
-      if (m == 0 && (t & 1)) mask[(row0 >> 1) + (t >> 1)] = (t < T_b) ? 1 : 0;
+      if (m4 == 0 && (t & 1)) mask[(row0 >> 1) + (t >> 1)] = (t < T_b) ? 1 : 0;
     }
   }
 };

@@ -47,12 +47,43 @@ AFE_HD void dft4(T& r0, T& i0, T& r1, T& i1, T& r2, T& i2, T& r3, T& i3) {
   r3 = t1r - t3i; i3 = t1i + t3r;      // t1 + i*t3
 }
 
+// dft4 with a3 = 0 (pruned: the frame has 400 samples, the transform 512 points)
+template <typename T>
+AFE_HD void dft4_a3zero(T& r0, T& i0, T& r1, T& i1, T& r2, T& i2, T& r3, T& i3) {
+  const T t0r = r0 + r2, t0i = i0 + i2, t1r = r0 - r2, t1i = i0 - i2;
+  r0 = t0r + r1; i0 = t0i + i1;
+  r2 = t0r - r1; i2 = t0i - i1;
+  r3 = t1r - i1; i3 = t1i + r1;        // t1 + i*a1   (before r1/i1 are overwritten)
+  const T nr1 = t1r + i1, ni1 = t1i - r1;      // t1 - i*a1
+  r1 = nr1; i1 = ni1;
+}
+// dft4 with Im(a3) = 0
+template <typename T>
+AFE_HD void dft4_i3zero(T& r0, T& i0, T& r1, T& i1, T& r2, T& i2, T& r3, T& i3) {
+  const T t0r = r0 + r2, t0i = i0 + i2, t1r = r0 - r2, t1i = i0 - i2;
+  const T t2r = r1 + r3, t3r = r1 - r3;
+  r0 = t0r + t2r; i0 = t0i + i1;
+  r2 = t0r - t2r; i2 = t0i - i1;
+  r3 = t1r - i1; i3 = t1i + t3r;
+  const T nr1 = t1r + i1, ni1 = t1i - t3r;
+  r1 = nr1; i1 = ni1;
+}
+
 // 16-point complex FFT, natural order in, natural order out.
 //   n = 4*n1 + n2, k = k1 + 4*k2:  X[k1+4k2] = sum_n2 W16^(n2 k1) W4^(n2 k2) sum_n1 x[4n1+n2] W4^(n1 k1)
-template <typename T> AFE_HD void fft16(T (&re)[16], T (&im)[16]) {
+//   kTailZero: inputs 13, 14, 15 and Im(input 12) are zero (stage 1 of the 400-sample frame);
+//   the first pass then skips their additions (x + 0.0 is not foldable under IEEE rules).
+template <typename T, bool kTailZero = false> AFE_HD void fft16(T (&re)[16], T (&im)[16]) {
+  if (kTailZero) {
+    dft4_i3zero(re[0], im[0], re[4], im[4], re[8], im[8], re[12], im[12]);
 #pragma unroll
-  for (int n2 = 0; n2 < 4; ++n2)       // a[n2][k1] stored at index 4*k1 + n2
-    dft4(re[n2], im[n2], re[4 + n2], im[4 + n2], re[8 + n2], im[8 + n2], re[12 + n2], im[12 + n2]);
+    for (int n2 = 1; n2 < 4; ++n2)
+      dft4_a3zero(re[n2], im[n2], re[4 + n2], im[4 + n2], re[8 + n2], im[8 + n2], re[12 + n2], im[12 + n2]);
+  } else {
+#pragma unroll
+    for (int n2 = 0; n2 < 4; ++n2)     // a[n2][k1] stored at index 4*k1 + n2
+      dft4(re[n2], im[n2], re[4 + n2], im[4 + n2], re[8 + n2], im[8 + n2], re[12 + n2], im[12 + n2]);
+  }
 #pragma unroll
   for (int k1 = 1; k1 < 4; ++k1)
 #pragma unroll

@@ -154,42 +154,44 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // Kernels with kAsyncStage provide
 //   bool stage_src(const Item&, const float*& src, int& nfloats)   true -> the item's staging
 //        (phase 0) is one contiguous 16-byte-aligned copy of nfloats (multiple of 4) floats
+//   Item next(const Item& cur, long item)   the context of item `item` = cur.item + 1, derived
+//        incrementally (no search: the next tile of the same waveform, or the next waveform)
 //   kStageOff / kStageBytes: two staging buffers back to back at kStageOff; Item::buf picks one.
-// The driver prefetches item i+1 with ONE TMA bulk copy while item i computes; items whose
-// staging is not a plain copy (edges, unaligned pointers) run phase 0 cooperatively.
+// A block owns a CONTIGUOUS range of items.  Thread 0 derives item i+1 from item i, publishes
+// it through shared memory and issues its TMA copy while everybody computes item i; the wait
+// on the copy's mbarrier is the only synchronisation before phase 1.  Items whose staging is
+// not a plain copy (edges, unaligned pointers) run phase 0 cooperatively.
 template <class K>
 __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(const K k) {
   extern __shared__ __align__(16) unsigned char afe_smem[];
   const long n = k.num_items();
   const int tid = (int)threadIdx.x;
   if constexpr (K::kAsyncStage) {
-    // thread 0 prepares item i+1 (tile lookup), publishes it through shared memory and
-    // issues its TMA copy while everybody computes item i.
     __shared__ __align__(8) uint64_t bars[2];
     __shared__ typename K::Item items[2];
-    long item = blockIdx.x;
+    const long per = (n + gridDim.x - 1) / gridDim.x;
+    long item = (long)blockIdx.x * per;
+    const long end = (item + per < n) ? item + per : n;
+    if (item >= end) return;
     if (tid == 0) {
       mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_mbar_init();
-      if (item < n) {
-        typename K::Item c0 = k.prepare(item);
-        c0.buf = 0;
-        const float* src; int nf;
-        c0.bulk = k.stage_src(c0, src, nf) ? 1 : 0;
-        items[0] = c0;
-        if (c0.bulk) {
-          mbar_expect_tx(&bars[0], (uint32_t)nf * 4u);
-          bulk_g2s(afe_smem + K::kStageOff, src, (uint32_t)nf * 4u, &bars[0]);
-        }
+      typename K::Item c0 = k.prepare(item);
+      c0.buf = 0;
+      const float* src; int nf;
+      c0.bulk = k.stage_src(c0, src, nf) ? 1 : 0;
+      items[0] = c0;
+      if (c0.bulk) {
+        mbar_expect_tx(&bars[0], (uint32_t)nf * 4u);
+        bulk_g2s(afe_smem + K::kStageOff, src, (uint32_t)nf * 4u, &bars[0]);
       }
     }
     __syncthreads();
     uint32_t par[2] = {0u, 0u};
-    for (int it = 0; item < n; item += gridDim.x, ++it) {
+    for (int it = 0; item < end; ++item, ++it) {
       const int buf = it & 1;
       const typename K::Item cur = items[buf];
-      const long next = item + gridDim.x;
-      if (tid == 0 && next < n) {
-        typename K::Item nx = k.prepare(next);
+      if (tid == 0 && item + 1 < end) {
+        typename K::Item nx = k.next(cur, item + 1);
         nx.buf = buf ^ 1;
         const float* src; int nf;
         nx.bulk = k.stage_src(nx, src, nf) ? 1 : 0;
@@ -201,8 +203,7 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
         }
       }
       if (cur.bulk) { mbar_wait(&bars[buf], par[buf]); par[buf] ^= 1u; }
-      else k.phase(0, cur, afe_smem, tid);
-      __syncthreads();
+      else { k.phase(0, cur, afe_smem, tid); __syncthreads(); }
 #pragma unroll
       for (int ph = 1; ph < K::kPhases; ++ph) {
         k.phase(ph, cur, afe_smem, tid);
@@ -247,15 +248,27 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
   std::vector<double> backing((smem_bytes + 64) / sizeof(double) + 2);   // 8-byte aligned, zeroed
   unsigned char* smem = reinterpret_cast<unsigned char*>(backing.data());
   long grid = n < (long)max_blocks ? n : (long)max_blocks;
-  for (long block = 0; block < grid; ++block) {
-    int it = 0;
-    for (long item = block; item < n; item += grid, ++it) {
-      typename K::Item ic = k.prepare(item);
-      ic.buf = K::kAsyncStage ? (it & 1) : 0;          // exercise both staging buffers
-      ic.bulk = 0;
-      for (int ph = 0; ph < K::kPhases; ++ph)
-        for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
+  if constexpr (K::kAsyncStage) {
+    if (grid > 3) grid = 3;                              // long ranges: next() crosses waveforms
+    const long per = (n + grid - 1) / grid;              // contiguous ranges, items derived by next()
+    for (long block = 0; block < grid; ++block) {
+      const long first = block * per, end = first + per < n ? first + per : n;
+      typename K::Item ic{};
+      for (long item = first; item < end; ++item) {
+        ic = (item == first) ? k.prepare(item) : k.next(ic, item);
+        ic.buf = (int)((item - first) & 1);              // exercise both staging buffers
+        ic.bulk = 0;
+        for (int ph = 0; ph < K::kPhases; ++ph)
+          for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
+      }
     }
+  } else {
+    for (long block = 0; block < grid; ++block)
+      for (long item = block; item < n; item += grid) {
+        typename K::Item ic = k.prepare(item);
+        for (int ph = 0; ph < K::kPhases; ++ph)
+          for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
+      }
   }
   return 0;
 }

@@ -48,7 +48,7 @@ AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRIC
   re[12] = r[24]; im[12] = T(0);
 #pragma unroll
   for (int m = 13; m < 16; ++m) { re[m] = T(0); im[m] = T(0); }
-  fft16(re, im);
+  fft16<T, true>(re, im);
   // untangle the packed real transform (inputs were pre-scaled by 1/2)
   const T r0 = T(2) * (re[0] + im[0]);
   const T r16 = T(2) * (re[0] - im[0]);

@@ -227,7 +227,8 @@ int afe_create(int device, afe_ctx** out) {
     ok = ok && (c->htk_mel_dev.up = c->upload(htk.up)) && (c->htk_mel_dev.dn = c->upload(htk.dn)) &&
          (c->htk_mel_dev.iv_start = c->upload(htk.iv_start)) && (c->htk_mel_dev.iv_count = c->upload(htk.iv_count)) &&
          (c->htk_mel_dev.role_iv = c->upload(htk.role_iv));
-    ok = ok && (c->d_dct = c->upload(make_dct_matrix()));
+    c->h_dct = make_dct_matrix();
+    ok = ok && (c->d_dct = c->upload(c->h_dct));
     c->log_floor = (float)std::log((double)kMelFloor);
   }
 #if AFE_CUDA

@@ -94,14 +94,34 @@ class CallFrontend:
         main = torch.cuda.current_stream(dev)
         if any_host and self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(dev)
-        uploads = []                                              # (device tensors, ready event) per sub-batch
+        # Device copies of host calls live in ONE buffer allocated on the compute stream (so the
+        # caching allocator never has to cudaMalloc / defer a free on the side stream); the
+        # copy stream first waits for the compute stream to reach this point.
+        xdev: List[Optional[torch.Tensor]] = [None] * len(calls)
+        if any_host:
+            offs, total = [], 0
+            for c in calls:
+                offs.append(total)
+                if not c.is_cuda:
+                    total += (c.numel() + 3) // 4 * 4
+            xin = torch.empty((max(total, 1),), dtype=torch.float32, device=dev)
+            for i, c in enumerate(calls):
+                if not c.is_cuda:
+                    xdev[i] = xin[offs[i]:offs[i] + c.numel()].view(c.shape)
+            self._copy_stream.wait_stream(main)
 
         def upload(k0):
-            sub = calls[k0:k0 + sb]
+            sub = range(k0, min(k0 + sb, len(calls)))
             if not any_host:
-                return [c.to(dev) for c in sub], None
+                return [calls[i].to(dev) for i in sub], None
+            xs = []
             with torch.cuda.stream(self._copy_stream):
-                xs = [c.to(dev, non_blocking=True) for c in sub]
+                for i in sub:
+                    if xdev[i] is None:
+                        xs.append(calls[i].to(dev))
+                    else:
+                        xdev[i].copy_(calls[i], non_blocking=True)
+                        xs.append(xdev[i])
                 ev = torch.cuda.Event()
                 ev.record(self._copy_stream)
             return xs, ev
@@ -115,9 +135,6 @@ class CallFrontend:
                 pending = upload(starts[si + 1])                  # enqueue the next upload before this compute
             if ev is not None:
                 main.wait_event(ev)
-                for x in xs:
-                    if x.is_cuda:
-                        x.record_stream(main)
             # resample / mix: stereo and mono calls of the sub-batch, one launch each
             for want_rows in (2, 1):
                 ids = [k0 + j for j, x in enumerate(xs) if int(x.shape[0]) == want_rows]

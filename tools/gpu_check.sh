@@ -11,7 +11,8 @@ python bench.py --steps 5 --warmup 3 > $O/bench_line.json 2> $O/bench.err; echo 
 cat $O/bench_line.json
 python tools/microbench.py > $O/microbench.json 2> $O/microbench.err; echo "microbench exit $?"
 cat $O/microbench.json
-if [ "${2:-}" != "skip-ncu" ]; then
+MODE=${2:-all}
+if [ "$MODE" != "skip-ncu" ]; then
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/plain_bench.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file $O/bench_launches.csv \
       python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/ncu_bench.log 2>&1
@@ -20,7 +21,7 @@ if [ "${2:-}" != "skip-ncu" ]; then
   ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:FbankKernel.double \
       -s 3 -c 1 -o $O/fbank_f64 python tools/microbench.py --only fbank_f64 --reps 1 > $O/ncu_fbank.log 2>&1
   echo "ncu fbank exit $?"
-  python tools/microbench.py --only acoustic --reps 1 > $O/plain_mb2.log 2>&1 &&
+  [ "$MODE" = "all" ] && python tools/microbench.py --only acoustic --reps 1 > $O/plain_mb2.log 2>&1 &&
   ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:AcousticTileKernel \
       -s 3 -c 1 -o $O/acoustic_tile python tools/microbench.py --only acoustic --reps 1 > $O/ncu_acoustic.log 2>&1
   echo "ncu acoustic exit $?"
