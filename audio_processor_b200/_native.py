@@ -63,6 +63,10 @@ SIGNATURES = {
     "afe_resample_batch_workspace_bytes": (C.c_size_t, [C.c_int]),
     "afe_resample_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int, C.c_int,
                                      C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_size_t]),
+    "afe_resample_batch_pcm16": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
+                                           C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p,
+                                           C.c_size_t]),
+    "afe_pcm16_to_float": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "afe_mix_stereo": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "afe_fbank_layout": (C.c_int, [c_i64p, C.c_int, C.c_int, c_i64p, c_i64p]),
     "afe_fbank_workspace_bytes": (C.c_size_t, [c_i64p, C.c_int]),

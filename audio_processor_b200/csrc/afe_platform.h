@@ -32,6 +32,7 @@
 typedef void* cudaStream_t;
 struct alignas(8) float2 { float x, y; };
 struct alignas(16) float4 { float x, y, z, w; };
+struct alignas(8) short4 { short x, y, z, w; };
 #endif
 
 namespace afe {

@@ -22,21 +22,37 @@ struct MixKernel {
     }
   }
 };
+// float32 = int16 / 32768 (what torchaudio.load(normalize=True) returns for 16-bit PCM)
+struct Pcm16Kernel {
+  static constexpr int kThreads = 256;
+  static constexpr int kMinBlocks = 8;
+  static constexpr int kPhases = 1;
+  static constexpr int kItem = 4096;
+  const int16_t* in; float* out; int64_t n;
+  AFE_PLAIN_ITEM
+  AFE_HD long num_items() const { return (long)((n + kItem - 1) / kItem); }
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    for (int v = tid; v < kItem; v += kThreads) {
+      const int64_t i = it.item * kItem + v;
+      if (i < n) out[i] = (float)in[i] * (1.0f / 32768.0f);
+    }
+  }
+};
 }  // namespace afe
 
 namespace {
 // one launch of the 1:2 kernel over `ncalls` calls (device descriptors) or the inline call
 int launch_up2x(afe_ctx* ctx, cudaStream_t s, const ResampleTaps& t, const UpCall* d_calls, const UpCall& one,
-                int ncalls, int rows, bool stereo_mix, long nitems = -1) {
+                int ncalls, int rows, bool stereo_mix, long nitems = -1, bool pcm16 = false) {
   if (nitems < 0) nitems = (long)((one.L + 1023) / 1024) * (stereo_mix ? 1 : rows);
   if (stereo_mix) {
     Upsample2xKernel<true> k;
-    k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = 2; k.nitems = nitems;
+    k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = 2; k.nitems = nitems; k.pcm16 = pcm16 ? 1 : 0;
     for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
     return afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * 8, s);
   }
   Upsample2xKernel<false> k;
-  k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = rows; k.nitems = nitems;
+  k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = rows; k.nitems = nitems; k.pcm16 = pcm16 ? 1 : 0;
   for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
   return afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * 8, s);
 }
@@ -99,9 +115,36 @@ size_t afe_resample_batch_workspace_bytes(int ncalls) {
   return (sizeof(UpCall) * (size_t)(ncalls > 0 ? ncalls : 1) + 255) / 256 * 256;
 }
 
+int afe_pcm16_to_float(afe_ctx* ctx, void* stream, const int16_t* d_in, int64_t count, float* d_out) {
+  if (!ctx || count < 0 || (count > 0 && (!d_in || !d_out))) return fail(AFE_ERR_INVALID, "afe_pcm16_to_float: bad arguments");
+  if (count == 0) return AFE_OK;
+  Pcm16Kernel k{d_in, d_out, count};
+  ProfScope ps(ctx, AFE_K_MIX, (cudaStream_t)stream);
+  if (afe_launch(k, 0, ctx->num_sms * 8, (cudaStream_t)stream) != 0) return fail(AFE_ERR_CUDA, "afe_pcm16_to_float: launch failed");
+  return AFE_OK;
+}
+
+static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_in, bool pcm16, const int64_t* h_lengths,
+                               int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                               float* const* h_mixed, void* d_workspace, size_t workspace_bytes);
+
 int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, const int64_t* h_lengths, int ncalls,
                        int rows, int orig_hz, int new_hz, float* const* h_out, float* const* h_mixed,
                        void* d_workspace, size_t workspace_bytes) {
+  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), false, h_lengths, ncalls, rows,
+                             orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
+}
+
+int afe_resample_batch_pcm16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
+                             int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                             float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
+  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), true, h_lengths, ncalls, rows,
+                             orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
+}
+
+static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_in, bool pcm16, const int64_t* h_lengths,
+                               int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                               float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
   if (!ctx || ncalls < 0 || rows <= 0 || orig_hz <= 0 || new_hz <= 0)
     return fail(AFE_ERR_INVALID, "afe_resample_batch: bad arguments");
   if (ncalls == 0) return AFE_OK;
@@ -111,10 +154,13 @@ int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, con
   const DeviceTaps* dt = ctx->get_taps(orig_hz, new_hz);
   if (!dt) return AFE_ERR_CUDA;
   const ResampleTaps& t = dt->host;
-  if (!(t.O == 1 && t.N == 2 && t.K == 15) || ncalls == 1) {
+  if (pcm16 && !(t.O == 1 && t.N == 2 && t.K == 15))
+    return fail(AFE_ERR_UNSUPPORTED, "afe_resample_batch_pcm16: only the 1:2 rate pair stages PCM directly; "
+                                     "convert with afe_pcm16_to_float first");
+  if (!pcm16 && (!(t.O == 1 && t.N == 2 && t.K == 15) || ncalls == 1)) {
     // other rate pairs: one launch per call through the generic path
     for (int c = 0; c < ncalls; ++c) {
-      const int rc = afe_resample(ctx, stream, h_in[c], rows, h_lengths[c], orig_hz, new_hz, h_out[c],
+      const int rc = afe_resample(ctx, stream, static_cast<const float*>(h_in[c]), rows, h_lengths[c], orig_hz, new_hz, h_out[c],
                                   h_mixed ? h_mixed[c] : nullptr, resampled_length(h_lengths[c], orig_hz, new_hz));
       if (rc != AFE_OK) return rc;
     }
@@ -131,7 +177,7 @@ int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, con
   bool bad = false;
   for (int c = 0; c < ncalls; ++c) {
     if (h_lengths[c] < 0 || (h_lengths[c] > 0 && (!h_in[c] || !h_out[c] || (mix && !h_mixed[c])))) bad = true;
-    hc[c] = UpCall{h_in[c], h_out[c], mix ? h_mixed[c] : nullptr, h_lengths[c], (int64_t)items};
+    hc[c] = UpCall{static_cast<const float*>(h_in[c]), h_out[c], mix ? h_mixed[c] : nullptr, h_lengths[c], (int64_t)items};
     items += (long)((h_lengths[c] + 1023) / 1024) * (mix ? 1 : rows);
   }
   if (bad) { ctx->staging_submit(blk, s); return fail(AFE_ERR_INVALID, "afe_resample_batch: NULL buffer or negative length"); }
@@ -141,7 +187,7 @@ int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, con
   int rc;
   {
     ProfScope ps(ctx, AFE_K_RESAMPLE, s);
-    rc = launch_up2x(ctx, s, t, static_cast<const UpCall*>(d_workspace), UpCall{}, ncalls, rows, mix, items);
+    rc = launch_up2x(ctx, s, t, static_cast<const UpCall*>(d_workspace), UpCall{}, ncalls, rows, mix, items, pcm16);
   }
   if (rc != 0) return fail(AFE_ERR_CUDA, std::string("afe_resample_batch: launch failed: ") + dev_last_error_string());
   return AFE_OK;

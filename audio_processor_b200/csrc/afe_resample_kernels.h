@@ -38,6 +38,7 @@ template <bool STEREO> struct Upsample2xKernel {
   UpCall one;
   int ncalls;
   int rows;               // rows per call (STEREO: 2)
+  int pcm16;              // inputs are int16 PCM (torchaudio.load's x / 32768 happens while staging)
   long nitems;
   float h[2][15];
 
@@ -66,7 +67,8 @@ template <bool STEREO> struct Upsample2xKernel {
     const int row0 = STEREO ? 0 : (int)(local / ipr);
     it.n0 = (int64_t)(local % ipr) * kPos;
     it.L = c.L;
-    it.src = c.in + (int64_t)row0 * c.L;
+    it.src = pcm16 ? reinterpret_cast<const float*>(reinterpret_cast<const int16_t*>(c.in) + (int64_t)row0 * c.L)
+                   : c.in + (int64_t)row0 * c.L;
     it.dst = c.out + (int64_t)row0 * 2 * c.L;
     it.mix = c.mixed;
     return it;
@@ -75,6 +77,28 @@ template <bool STEREO> struct Upsample2xKernel {
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     float* xs = reinterpret_cast<float*>(smem);
     const int64_t n0 = it.n0, L = it.L;
+    if (ph == 0 && pcm16) {
+      constexpr float kScale = 1.0f / 32768.0f;            // exact: the same value as x / 32768
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) {
+        const int16_t* src = reinterpret_cast<const int16_t*>(it.src) + (int64_t)r * L;
+        const int16_t* p0 = src + (n0 - 8);
+        if (n0 >= 8 && n0 - 8 + kTile <= L && (reinterpret_cast<uintptr_t>(p0) & 7u) == 0) {
+          const short4* s4 = reinterpret_cast<const short4*>(p0);
+          float4* d4 = reinterpret_cast<float4*>(xs + r * kTile);
+          for (int i = tid; i < kTile / 4; i += kThreads) {
+            const short4 v = s4[i];
+            d4[i] = float4{(float)v.x * kScale, (float)v.y * kScale, (float)v.z * kScale, (float)v.w * kScale};
+          }
+        } else {
+          for (int i = tid; i < kTile; i += kThreads) {
+            const int64_t g = n0 - 8 + i;
+            xs[r * kTile + i] = (g >= 0 && g < L) ? (float)src[g] * kScale : 0.f;
+          }
+        }
+      }
+      return;
+    }
     if (ph == 0) {
 #pragma unroll
       for (int r = 0; r < kRows; ++r) {

@@ -29,8 +29,30 @@ void dev_free(void* p) { if (p) cudaFree(p); }
 int dev_upload(void* dst, const void* src, size_t bytes) {
   return cuda_fail(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice), "cudaMemcpy H2D");
 }
+// Descriptor blocks travel in KERNEL PARAMETERS (through the launch queue), not through the
+// copy engine: a small cudaMemcpyAsync on the compute stream queues behind -- and, while it
+// waits for its own stream, blocks -- the bulk waveform uploads that run on another stream,
+// which serialises upload and compute (measured: no overlap at all).  16 KiB per launch.
+struct ParamBlob { uint4 q[1024]; };
+__global__ void __launch_bounds__(256) blob_store_kernel(const __grid_constant__ ParamBlob blob, unsigned char* dst, int nbytes) {
+  const int nq = nbytes >> 4;
+  uint4* d4 = reinterpret_cast<uint4*>(dst);
+  for (int i = (int)threadIdx.x; i < nq; i += (int)blockDim.x) d4[i] = blob.q[i];
+  const unsigned char* tail = reinterpret_cast<const unsigned char*>(blob.q);
+  for (int i = (nq << 4) + (int)threadIdx.x; i < nbytes; i += (int)blockDim.x) dst[i] = tail[i];
+}
 int dev_upload_async(void* dst, const void* src, size_t bytes, cudaStream_t s) {
-  return cuda_fail(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s), "cudaMemcpyAsync H2D");
+  if (bytes > (4u << 20) || (reinterpret_cast<uintptr_t>(dst) & 15u) != 0)
+    return cuda_fail(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s), "cudaMemcpyAsync H2D");
+  ParamBlob blob;
+  const unsigned char* p = static_cast<const unsigned char*>(src);
+  unsigned char* d = static_cast<unsigned char*>(dst);
+  for (size_t off = 0; off < bytes; off += sizeof(ParamBlob)) {
+    const size_t n = bytes - off < sizeof(ParamBlob) ? bytes - off : sizeof(ParamBlob);
+    std::memcpy(&blob, p + off, n);
+    blob_store_kernel<<<1, 256, 0, s>>>(blob, d + off, (int)n);
+  }
+  return cuda_fail(cudaGetLastError(), "descriptor upload launch");
 }
 int dev_memset_async(void* dst, int v, size_t bytes, cudaStream_t s) {
   return cuda_fail(cudaMemsetAsync(dst, v, bytes, s), "cudaMemsetAsync");

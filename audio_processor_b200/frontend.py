@@ -48,7 +48,10 @@ class CallFrontend:
 
     def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True,
                       sub_batch: Optional[int] = None) -> FrontendResult:
-        """``calls``: (C, L) float32 tensors (host -- ideally pinned -- or device).
+        """``calls``: (C, L) float32 waveforms, or int16 PCM as stored in a 16-bit wav file
+        (``torchaudio.load(..., normalize=False)``; converted on the device exactly like
+        ``torchaudio.load``'s ``x / 32768``, so a call crosses PCIe at 2 bytes per sample);
+        host -- ideally pinned -- or device tensors.
 
         Every integer of the result (chunk table, length-sorted order, the padded length of
         each batch of ``batch_size`` chunks, the output row of every chunk) depends on the call
@@ -99,15 +102,17 @@ class CallFrontend:
         # copy stream first waits for the compute stream to reach this point.
         xdev: List[Optional[torch.Tensor]] = [None] * len(calls)
         if any_host:
-            offs, total = [], 0
+            offs, total = [], 0                                   # in bytes, 16-byte aligned
             for c in calls:
                 offs.append(total)
                 if not c.is_cuda:
-                    total += (c.numel() + 3) // 4 * 4
-            xin = torch.empty((max(total, 1),), dtype=torch.float32, device=dev)
+                    total += (c.numel() * c.element_size() + 15) // 16 * 16
+            xin = torch.empty((max(total, 16),), dtype=torch.uint8, device=dev)
             for i, c in enumerate(calls):
                 if not c.is_cuda:
-                    xdev[i] = xin[offs[i]:offs[i] + c.numel()].view(c.shape)
+                    if c.dtype not in (torch.float32, torch.int16):
+                        raise TypeError("process_calls: calls must be float32 waveforms or int16 PCM")
+                    xdev[i] = xin[offs[i]:offs[i] + c.numel() * c.element_size()].view(c.dtype).view(c.shape)
             self._copy_stream.wait_stream(main)
 
         def upload(k0):
@@ -147,7 +152,7 @@ class CallFrontend:
                     else:
                         ys = fe.resample_batch(grp, sample_rate, sr_t); ms = ys
                 else:
-                    ys = [x.contiguous() for x in grp]
+                    ys = [fe.pcm16_to_float(x) if x.dtype == torch.int16 else x.contiguous() for x in grp]
                     ms = [fe.mix_stereo(y) for y in ys] if want_rows == 2 else ys
                 for i, y, m in zip(ids, ys, ms):
                     res.waveforms[i] = (y, m)

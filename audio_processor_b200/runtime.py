@@ -134,7 +134,10 @@ class Frontend:
         n = len(calls)
         if n == 0:
             return ([], []) if want_mixed else []
-        xs = [c.to(device=self.device, dtype=torch.float32).contiguous() for c in calls]
+        pcm16 = all(c.dtype == torch.int16 for c in calls)     # 16-bit PCM: x / 32768 while staging
+        if pcm16 and self.resampled_length(1000, orig, new) != 2000:
+            calls = [self.pcm16_to_float(c) for c in calls]; pcm16 = False
+        xs = [c.to(device=self.device, dtype=torch.int16 if pcm16 else torch.float32).contiguous() for c in calls]
         rows = int(xs[0].shape[0])
         if any(x.dim() != 2 or int(x.shape[0]) != rows for x in xs):
             raise ValueError("resample_batch: every call must be (rows, L) with the same number of rows")
@@ -155,13 +158,23 @@ class Frontend:
                 m = buf[o + rows * pad:o + rows * pad + lo].view(1, lo)
                 mixes.append(m); p_mix.append(m.data_ptr())
         ws = self._workspace3(int(self.lib.afe_resample_batch_workspace_bytes(n)))
+        fn = self.lib.afe_resample_batch_pcm16 if pcm16 else self.lib.afe_resample_batch
         with torch.cuda.device(self.device):
-            self.lib.check(self.lib.afe_resample_batch(
+            self.lib.check(fn(
                 self.ctx, self._stream(), _native.ptr_array([x.data_ptr() for x in xs]), _native.i64_array(lens), n,
                 rows, int(orig), int(new), _native.ptr_array(p_out), _native.ptr_array(p_mix) if want_mixed else None,
                 C.c_void_p(ws.data_ptr()), ws.numel()))
         self._tls.keep_rs = xs                      # inputs stay alive until the next call on this thread
         return (outs, mixes) if want_mixed else outs
+
+    def pcm16_to_float(self, x: torch.Tensor) -> torch.Tensor:
+        """int16 PCM -> float32 in [-1, 1): ``x / 32768`` (torchaudio.load's normalisation)."""
+        x = x.to(device=self.device, dtype=torch.int16).contiguous()
+        out = torch.empty(x.shape, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_pcm16_to_float(self.ctx, self._stream(), C.c_void_p(x.data_ptr()),
+                                                       int(x.numel()), C.c_void_p(out.data_ptr())))
+        return out
 
     def mix_stereo(self, x: torch.Tensor) -> torch.Tensor:
         x = x.to(device=self.device, dtype=torch.float32).contiguous()

@@ -91,6 +91,16 @@ int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, con
                        int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
                        float* const* h_mixed, void* d_workspace, size_t workspace_bytes);
 
+/* The same reading 16-bit PCM: h_in[c] points to int16 samples [rows, h_lengths[c]] on the
+ * device and x / 32768 -- torchaudio.load's normalisation (AudioProcessor.load_audio,
+ * services/audio_processor.py:72-93) -- is applied while the tile is staged, so a call
+ * crosses PCIe at 2 bytes per sample.  Only the 1:2 rate pair (8 k -> 16 k). */
+int afe_resample_batch_pcm16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
+                             int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                             float* const* h_mixed, void* d_workspace, size_t workspace_bytes);
+/* float32 = int16 / 32768 for `count` samples (other rate pairs, or no resampling at all) */
+int afe_pcm16_to_float(afe_ctx* ctx, void* stream, const int16_t* d_in, int64_t count, float* d_out);
+
 /* mixed = (row0 + row1) * 0.5 for waveforms that need no resampling (split_audio :123-131) */
 int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed);
 

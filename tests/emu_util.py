@@ -34,15 +34,16 @@ def resample(x, orig, new, want_mixed=False):
     return (out, mixed) if want_mixed else out
 
 
-def resample_batch(calls, orig, new, want_mixed=False):
+def resample_batch(calls, orig, new, want_mixed=False, pcm16=False):
     lib, ctx = emu()
-    calls = [np.ascontiguousarray(c, np.float32) for c in calls]
+    calls = [np.ascontiguousarray(c, np.int16 if pcm16 else np.float32) for c in calls]
     n, rows = len(calls), calls[0].shape[0]
     lens = [c.shape[1] for c in calls]
     outs = [np.full((rows, lib.afe_resampled_length(L, orig, new)), np.float32(-9.0), np.float32) for L in lens]
     mixes = [np.full((1, o.shape[1]), np.float32(-9.0), np.float32) for o in outs] if want_mixed else None
     ws = np.zeros(lib.afe_resample_batch_workspace_bytes(n), np.uint8)
-    lib.check(lib.afe_resample_batch(ctx, None, _native.ptr_array([c.ctypes.data for c in calls]),
+    fn = lib.afe_resample_batch_pcm16 if pcm16 else lib.afe_resample_batch
+    lib.check(fn(ctx, None, _native.ptr_array([c.ctypes.data for c in calls]),
                                      _native.i64_array(lens), n, rows, orig, new,
                                      _native.ptr_array([o.ctypes.data for o in outs]),
                                      _native.ptr_array([m.ctypes.data for m in mixes]) if want_mixed else None,

@@ -68,6 +68,20 @@ def test_emu_resample_batch_matches_per_call():
         assert np.array_equal(o, np_resample.resample(c, 16000, 8000))
 
 
+def test_emu_resample_pcm16_equals_float_path():
+    """int16 PCM staged as x / 32768 == resampling torchaudio.load's float32 waveform."""
+    rng = np.random.default_rng(13)
+    lens = [3, 1024, 1029, 2500, 4100]
+    pcm = [rng.integers(-32768, 32768, (2, L), dtype=np.int16) for L in lens]
+    outs, mixes = emu_util.resample_batch(pcm, 8000, 16000, want_mixed=True, pcm16=True)
+    for p, o, m in zip(pcm, outs, mixes):
+        ref = np_resample.resample(p.astype(np.float32) / np.float32(32768.0), 8000, 16000)
+        assert np.array_equal(o, ref)
+        assert np.array_equal(m[0], (ref[0] + ref[1]) * np.float32(0.5))
+    one = emu_util.resample_batch(pcm[3:4], 8000, 16000, pcm16=True)[0]       # single call, rows as items
+    assert np.array_equal(one, np_resample.resample(pcm[3].astype(np.float32) / np.float32(32768.0), 8000, 16000))
+
+
 def test_emu_resample_generic_rates():
     x = (np.random.default_rng(5).uniform(-0.5, 0.5, (1, 3000))).astype(np.float32)
     for orig, new in ((16000, 8000), (48000, 16000), (22050, 16000)):

@@ -289,3 +289,28 @@ def test_call_frontend_pipelined_equals_single_shot(fe):
     r16 = cf.process_calls([c16], 16000)
     ref_f, ref_m = np_fbank.featurise([((c16[0] + c16[1]) * 0.5).numpy()])
     _cmp_nan(r16.features["stereo"][0][0].cpu().numpy(), ref_f, 1e-3)
+
+
+def test_call_frontend_pcm16_ingest_is_bit_identical(fe):
+    """int16 PCM calls (2 bytes/sample over PCIe, x / 32768 on the device) give exactly the
+    tensors of the float32 waveforms torchaudio.load would have produced."""
+    import torch
+    from audio_processor_b200 import CallFrontend
+    g = torch.Generator().manual_seed(5)
+    pcm = [torch.randint(-20000, 20000, (2, n), generator=g, dtype=torch.int16) for n in (240000, 100003, 1000)]
+    flt = [p.to(torch.float32) / 32768.0 for p in pcm]
+    cf = CallFrontend(fe.device, batch_size=4)
+    a = cf.process_calls([p.pin_memory() for p in pcm], 8000, sub_batch=2)
+    b = cf.process_calls([f.pin_memory() for f in flt], 8000, sub_batch=2)
+    assert a.chunks == b.chunks
+    for (ya, ma), (yb, mb) in zip(a.waveforms, b.waveforms):
+        assert torch.equal(ya, yb) and torch.equal(ma, mb)
+    for key in ("stereo", "agent", "client"):
+        for (fa, ka), (fb, kb) in zip(a.features[key], b.features[key]):
+            assert torch.equal(fa, fb) and torch.equal(ka, kb)
+    assert torch.equal(a.acoustic_rows, b.acoustic_rows)
+    # 16 kHz PCM: no resampling, plain conversion
+    p16 = torch.randint(-20000, 20000, (2, 48000), generator=g, dtype=torch.int16)
+    c = cf.process_calls([p16], 16000)
+    d = cf.process_calls([p16.to(torch.float32) / 32768.0], 16000)
+    assert torch.equal(c.features["stereo"][0][0], d.features["stereo"][0][0])
