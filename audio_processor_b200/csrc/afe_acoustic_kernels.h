@@ -42,31 +42,42 @@ AFE_HD void ac_locate(const AcDesc& d, long item, int& b, int& t) {
   t = (int)(item - ldg(d.tile_prefix + lo));
 }
 
-constexpr int kHtkIv = kAcMel + 1;                // 129 intervals
-
 struct AcSmem {
   static constexpr size_t kRawBytes = sizeof(float) * kAcRaw;                    // 22272 per staging buffer
   static constexpr size_t kRawOff = 0;                                           // float[2][5568]
   static constexpr size_t kDOff = kRawOff + 2 * kRawBytes;                       // float[5536] padded copy
-  static constexpr size_t kSmallOff = kDOff + sizeof(float) * 5536;
-  // small arrays, in floats from kSmallOff (epart is double[512], 8-byte aligned)
-  static constexpr int kEp = 0;            // double[16][32] contiguous-range magnitude sums
-  static constexpr int kSq = 1024, kZc = 1360, kLast = 1696;        // [336] [336] [32]
-  static constexpr int kPc = 1728, kRed = 2240, kCnt = 2752, kBw = 3264, kFx = 3776;   // [512] each
-  static constexpr int kPf = 4288;         // [8][32] per-frame scalars
-  static constexpr size_t kSmallBytes = sizeof(float) * (4288 + 8 * 32);
-  static constexpr size_t kPOff = (kSmallOff + kSmallBytes + 15) / 16 * 16;      // float sP[257*32] -> magnitudes in place
-  static constexpr size_t kExOff = (kPOff + sizeof(float) * kBins * kTileFrames + 15) / 16 * 16;
-  //   ex region after stage 2: sU[129][32] sD[129][32] sDb[32][129]
-  static constexpr size_t kDbOff = kExOff + sizeof(float) * 2 * kHtkIv * kTileFrames;
+  static constexpr size_t kKeepOff = kDOff + sizeof(float) * 5536;               // sq16[336] zc16[336] lastx[32]
+  static constexpr int kSq = 0, kZc = 336, kLast = 672;
+  static constexpr size_t kPOff = (kKeepOff + sizeof(float) * 704 + 15) / 16 * 16;      // float sP[257*32] power
+  static constexpr size_t kMOff = kPOff + sizeof(float) * kBins * kTileFrames;           // float sM[257*32] magnitude
+  static constexpr size_t kExOff = (kMOff + sizeof(float) * kBins * kTileFrames + 15) / 16 * 16;
+  // the exchange region after stage 2: sDb[32][129] | double part[4][16][32] | float fx,red [16][32] | pf[8][32] | thr[32]
+  static constexpr size_t kDbOff = kExOff;
+  static constexpr size_t kPartOff = (kDbOff + sizeof(float) * kTileFrames * kDbStride + 15) / 16 * 16;
+  static constexpr size_t kFxOff = kPartOff + sizeof(double) * 4 * 512;
+  static constexpr size_t kRedOff = kFxOff + sizeof(float) * 512;
+  static constexpr size_t kPfOff = kRedOff + sizeof(float) * 512;
+  static constexpr size_t kThrOff = kPfOff + sizeof(float) * 8 * 32;
   static constexpr size_t kBytes = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;
-  static_assert(kDbOff + sizeof(float) * kTileFrames * kDbStride <= kBytes, "ex region too small");
+  static_assert(kThrOff + sizeof(float) * 64 <= kBytes, "ex region too small");
 };
+
+// sqrt for magnitudes: one MUFU (max relative error ~1 ulp); the reference's float32 |X| carries
+// the rounding noise of its own FFT, far above that.
+AFE_HD float mag_sqrt(float x) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return std::sqrt(x);
+#endif
+}
 
 struct AcousticTileKernel {
   static constexpr int kThreads = 512;
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 9;
+  static constexpr int kPhases = 8;
   static constexpr bool kAsyncStage = true;
   static constexpr size_t kStageOff = AcSmem::kRawOff;
   static constexpr size_t kStageBytes = AcSmem::kRawBytes;
@@ -74,7 +85,7 @@ struct AcousticTileKernel {
   struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int F1; int F2; int64_t L; const float* wave; int64_t row0; };
 
   AcDesc d;
-  const float* hann;        // [400] periodic Hann / 2
+  const float* hann;        // [16][26] role-major: periodic Hann[16 n1 + role] / 2
   const float* tw512;       // [16][16][2]
   float* meldb;             // [rows][128]
   double* tile_rec;         // [ntiles][16]
@@ -122,20 +133,32 @@ struct AcousticTileKernel {
 
   AFE_HD static bool crossing(float a, float c) { return (a > 0.f && c < 0.f) || (a < 0.f && c > 0.f); }
 
+  // (sum, sum of squares) of n <= 32 per-frame scalars, 4 independent chains when the tile is full
+  AFE_HD static void stat32(const float* v, int n, double& s, double& ss) {
+    double a[4] = {0.0, 0.0, 0.0, 0.0}, q[4] = {0.0, 0.0, 0.0, 0.0};
+    if (n == kTileFrames) {
+#pragma unroll
+      for (int j = 0; j < kTileFrames; ++j) { const double x = (double)v[j]; a[j & 3] += x; q[j & 3] += x * x; }
+    } else {
+      for (int j = 0; j < n; ++j) { const double x = (double)v[j]; a[0] += x; q[0] += x * x; }
+    }
+    s = (a[0] + a[1]) + (a[2] + a[3]); ss = (q[0] + q[1]) + (q[2] + q[3]);
+  }
+
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     float* raw = reinterpret_cast<float*>(smem + AcSmem::kRawOff + (size_t)it.buf * AcSmem::kRawBytes);
     float* dbuf = reinterpret_cast<float*>(smem + AcSmem::kDOff);
-    float* small = reinterpret_cast<float*>(smem + AcSmem::kSmallOff);
-    float* sP = reinterpret_cast<float*>(smem + AcSmem::kPOff);        // power, then magnitude in place
+    float* keep = reinterpret_cast<float*>(smem + AcSmem::kKeepOff);
+    float* sP = reinterpret_cast<float*>(smem + AcSmem::kPOff);        // power
+    float* sM = reinterpret_cast<float*>(smem + AcSmem::kMOff);        // magnitude
     cplx<float>* ex = reinterpret_cast<cplx<float>*>(smem + AcSmem::kExOff);
-    float* sU = reinterpret_cast<float*>(smem + AcSmem::kExOff);
-    float* sD = sU + kHtkIv * kTileFrames;
     float* sDb = reinterpret_cast<float*>(smem + AcSmem::kDbOff);
-    double* epart = reinterpret_cast<double*>(small + AcSmem::kEp);
-    float* sq16 = small + AcSmem::kSq;  float* zc16 = small + AcSmem::kZc;  float* lastx = small + AcSmem::kLast;
-    float* pc = small + AcSmem::kPc;    float* red = small + AcSmem::kRed;
-    float* cntp = small + AcSmem::kCnt; float* bwp = small + AcSmem::kBw;   float* fxp = small + AcSmem::kFx;
-    float* pf = small + AcSmem::kPf;    // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax [7]=energy
+    double* part = reinterpret_cast<double*>(smem + AcSmem::kPartOff);  // [0] e  [1] sum m k  [2] sum m k^2  [3] exclusive prefix of e
+    float* fxp = reinterpret_cast<float*>(smem + AcSmem::kFxOff);
+    float* red = reinterpret_cast<float*>(smem + AcSmem::kRedOff);
+    float* pf = reinterpret_cast<float*>(smem + AcSmem::kPfOff);       // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
+    float* thrs = reinterpret_cast<float*>(smem + AcSmem::kThrOff);    // [0] threshold  [1] total (float)
+    float* sq16 = keep + AcSmem::kSq;  float* zc16 = keep + AcSmem::kZc;  float* lastx = keep + AcSmem::kLast;
     const int role = tid >> 5, f = tid & 31;
     const int kb = role * 16, ke = (role == 15) ? kBins : kb + 16;       // contiguous bin range of this role
 
@@ -150,7 +173,13 @@ struct AcousticTileKernel {
         }
       } break;
       case 1: {   // padded copy for the STFT + 16-sample partials of the unfold frames
-        for (int i = tid; i < kTileSamples; i += kThreads) dbuf[phys_idx(i)] = raw[i];
+        {         // element i = tid + 512 j sits at i + (i >> 5) = tid + role + 528 j
+          float* dp = dbuf + tid + role;
+          const float* rp = raw + tid;
+#pragma unroll
+          for (int j = 0; j < kTileSamples / kThreads; ++j) dp[(kThreads + 16) * j] = rp[kThreads * j];
+          if (tid < kTileSamples % kThreads) dp[(kThreads + 16) * (kTileSamples / kThreads)] = rp[kThreads * (kTileSamples / kThreads)];
+        }
         if (tid < kGroups16) {
           float s = 0.f, z = 0.f;
 #pragma unroll
@@ -167,115 +196,124 @@ struct AcousticTileKernel {
       } break;
       case 2: {   // Hann window + stage 1 of the real FFT
         float r[25];
-#pragma unroll
-        for (int n1 = 0; n1 < 25; ++n1) {
-          const int n = 16 * n1 + role;
-          r[n1] = ldg(hann + n) * dbuf[phys_idx(kHop * f + n)];
-        }
+        const float* col = dbuf + (kHop + kHop / 32) * f + role;  // phys_idx(160 f + 16 n1 + role) = 165 f + role + 16 n1 + (n1 >> 1)
+        windowed_column<float>(hann + role * kWinRow, r, [col](int n1) { return col[16 * n1 + (n1 >> 1)]; });
         rfft512_stage1<float>(r, role, f, tw512, ex);
       } break;
-      case 3:
-        rfft512_stage2<float>(role, f, ex, sP);
+      case 3:     // stage 2: power (mel bank) and magnitude (spectral features)
+        rfft512_stage2<float, true>(role, f, ex, sP, sM);
         break;
-      case 4:     // 128 HTK mel filters, interval form (reads the POWER spectrum)
-        mel_intervals_htk(role, f, sP, sU, sD);
-        break;
-      case 5: {   // dB rows; magnitudes in place + contiguous-range sums
+      case 4: {   // 128 HTK mel filters -> dB rows; moments / flux of this role's contiguous bins
         float mx = -3.0e38f;
-#pragma unroll
-        for (int m = role; m < kAcMel; m += kRoles) {
-          const float acc = sU[m * kTileFrames + f] + sD[(m + 1) * kTileFrames + f];
+        float* row = sDb + f * kDbStride;
+        mel_filters_htk(role, f, sP, [row, &mx](int m, float acc) {
           const float db = 10.f * fast_log10(tmax(acc, 1e-10f));
-          sDb[f * kDbStride + m] = db;
+          row[m] = db;
           mx = tmax(mx, db);
-        }
+        });
         red[tid] = mx;
-        double e = 0.0;
-        float c = 0.f;
-        for (int k = kb; k < ke; ++k) {
-          const float m = fast_sqrt(sP[k * kTileFrames + f]);
-          sP[k * kTileFrames + f] = m;
-          e += (double)m; c = fma_f(m, (float)k, c);
-        }
-        epart[role * 32 + f] = e; pc[role * 32 + f] = c;
-      } break;
-      case 6: {   // per-frame totals, then this role's share of rolloff / bandwidth / flux
-        double tot = 0.0, pre = 0.0;
-        float c = 0.f;
-#pragma unroll
-        for (int r = 0; r < kRoles; ++r) {
-          if (r == role) pre = tot;
-          tot += epart[r * 32 + f]; c += pc[r * 32 + f];
-        }
-        const float total = (float)tot;                  // cum_energy[-1] (float64 accumulate like ATen's cumsum)
-        const float energy = total + 1e-8f;
-        const float cen = 31.25f * c / energy;
-        const float thr = 0.85f * (total + 1e-8f);
-        double acc = pre;
-        int below = 0;
-        float bw = 0.f, fx = 0.f;
+        double e = 0.0, c = 0.0, c2 = 0.0, kd = (double)kb;
+        float fx = 0.f;
         const bool has_next = (f + 1 < it.nvalid);
-        for (int k = kb; k < ke; ++k) {
-          const float m = sP[k * kTileFrames + f];
-          acc += (double)m;
-          below += ((float)acc < thr) ? 1 : 0;
-          const float df = 31.25f * (float)k - cen;
-          bw = fma_f(m, df * df, bw);
-          if (has_next) fx += tmax(sP[k * kTileFrames + f + 1] - m, 0.f);
+        if (role < 15) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float m = sM[(kb + j) * kTileFrames + f];
+            const double md = (double)m, t = md * kd;
+            e += md; c += t; c2 += t * kd; kd += 1.0;
+            if (has_next) fx += tmax(sM[(kb + j) * kTileFrames + f + 1] - m, 0.f);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 17; ++j) {
+            const float m = sM[(kb + j) * kTileFrames + f];
+            const double md = (double)m, t = md * kd;
+            e += md; c += t; c2 += t * kd; kd += 1.0;
+            if (has_next) fx += tmax(sM[(kb + j) * kTileFrames + f + 1] - m, 0.f);
+          }
         }
-        cntp[role * 32 + f] = (float)below; bwp[role * 32 + f] = bw; fxp[role * 32 + f] = fx;
-        if (role == 0) { pf[0 * 32 + f] = cen; pf[7 * 32 + f] = energy; }
-        if (role == 1) {
+        part[0 * 512 + tid] = e; part[1 * 512 + tid] = c; part[2 * 512 + tid] = c2; fxp[tid] = fx;
+      } break;
+      case 5: {   // per-frame scalars: warp 0 spectral totals, warp 1 rms / zcr, warp 2 max dB
+        if (role == 0) {
+          double tot = 0.0, C = 0.0, C2 = 0.0;
+          float fx = 0.f;
+#pragma unroll
+          for (int r = 0; r < kRoles; ++r) {
+            part[3 * 512 + r * 32 + f] = tot;               // exclusive prefix: cum_energy before role r's bins
+            tot += part[0 * 512 + r * 32 + f]; C += part[1 * 512 + r * 32 + f]; C2 += part[2 * 512 + r * 32 + f];
+            fx += fxp[r * 32 + f];
+          }
+          const float total = (float)tot;                  // cum_energy[-1] (float64 accumulate like ATen's cumsum)
+          const float energy = total + 1e-8f;
+          const float cen = 31.25f * (float)C / energy;
+          // sum m (31.25 k - cen)^2 from the three moments, in float64
+          const double cd = (double)cen;
+          const double num = (31.25 * 31.25) * C2 - 2.0 * 31.25 * cd * C + cd * cd * tot;
+          pf[0 * 32 + f] = cen;
+          pf[1 * 32 + f] = fast_sqrt((float)(num > 0.0 ? num : 0.0) / energy);
+          pf[3 * 32 + f] = fx;
+          thrs[f] = 0.85f * (total + 1e-8f);
+          thrs[32 + f] = total;
+        } else if (role == 1) {
           float s = 0.f, z = 0.f;
 #pragma unroll
           for (int g = 0; g < 25; ++g) { s += sq16[10 * f + g]; z += zc16[10 * f + g]; }
           pf[4 * 32 + f] = fast_sqrt(s / 400.f);
           pf[5 * 32 + f] = (z - lastx[f]) / 400.f;
-        }
-        if (role == 2) {
+        } else if (role == 2) {
           float mx = -3.0e38f;
 #pragma unroll
           for (int r = 0; r < kRoles; ++r) mx = tmax(mx, red[r * 32 + f]);
           pf[6 * 32 + f] = mx;
         }
       } break;
-      case 7: {   // combine the 16 partials per frame
-        if (role < 3) {
-          float s = 0.f;
-          const float* src = (role == 0) ? cntp : (role == 1) ? bwp : fxp;
-#pragma unroll
-          for (int r = 0; r < kRoles; ++r) s += src[r * 32 + f];
-          if (role == 0) pf[2 * 32 + f] = 31.25f * ((s >= (float)kBins) ? 0.f : s);
-          else if (role == 1) pf[1 * 32 + f] = fast_sqrt(s / pf[7 * 32 + f]);
-          else pf[3 * 32 + f] = s;
+      case 6: {   // rolloff: only the role whose bin range holds the 85 % crossing scans its bins
+        const float thr = thrs[f];
+        const double lo = part[3 * 512 + tid];
+        const double hi = lo + part[0 * 512 + tid];         // == the next role's prefix (same additions)
+        const bool lo_below = (role == 0) || ((float)lo < thr);
+        const bool hi_below = ((float)hi < thr);
+        if (role == 15 && hi_below) {
+          pf[2 * 32 + f] = 0.f;                             // no bin reaches the threshold: argmax of all-False is 0
+        } else if (lo_below && !hi_below) {
+          double acc = lo;
+          int below = 0;
+          for (int k = kb; k < ke; ++k) {
+            acc += (double)sM[k * kTileFrames + f];
+            if (!((float)acc < thr)) break;
+            ++below;
+          }
+          pf[2 * 32 + f] = 31.25f * (float)(kb + below);
         }
       } break;
-      case 8: {   // tile record, boundary spectra, mel-dB rows
+      case 7: {   // tile record, boundary spectra, mel-dB rows
         double* rec = tile_rec + it.item * kTileRec;
         if (tid < 5) {          // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff
           const int src = (tid == 0) ? 4 : (tid == 1) ? 5 : (tid - 2);
           const int n = (tid < 2) ? tmax(0, tmin(kTileFrames, it.F1 - it.f0)) : it.nvalid;
-          double s = 0.0, ss = 0.0, mn = 3.0e38, mxv = -3.0e38;
-          for (int j = 0; j < n; ++j) {
-            const double v = (double)pf[src * 32 + j];
-            s += v; ss += v * v; mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv;
-          }
+          double s, ss;
+          stat32(pf + src * 32, n, s, ss);
           rec[2 * tid] = s; rec[2 * tid + 1] = ss;
-          if (tid == 0) { rec[11] = mn; rec[12] = mxv; }
-        } else if (tid == 5) {
+        } else if (tid == 32) {  // rms range
+          const int n = tmax(0, tmin(kTileFrames, it.F1 - it.f0));
+          double mn = 3.0e38, mxv = -3.0e38;
+          for (int j = 0; j < n; ++j) { const double v = (double)pf[4 * 32 + j]; mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv; }
+          rec[11] = mn; rec[12] = mxv;
+        } else if (tid == 64) {
           double s = 0.0;
           for (int j = 0; j + 1 < it.nvalid; ++j) { const double v = (double)pf[3 * 32 + j]; s += v * v; }
           rec[10] = s;
-        } else if (tid == 6) {
+        } else if (tid == 96) {
           float mx = -3.0e38f;
           for (int j = 0; j < it.nvalid; ++j) mx = tmax(mx, pf[6 * 32 + j]);
           rec[13] = (double)mx;
         }
-        if (tid >= 64 && tid < 64 + kBins) {
-          const int k = tid - 64;
+        if (tid >= 128 && tid < 128 + kBins) {
+          const int k = tid - 128;
           float* bd = boundary + it.item * 2 * kBoundary;
-          bd[k] = sP[k * kTileFrames + 0];
-          bd[kBoundary + k] = sP[k * kTileFrames + (it.nvalid - 1)];
+          bd[k] = sM[k * kTileFrames + 0];
+          bd[kBoundary + k] = sM[k * kTileFrames + (it.nvalid - 1)];
         }
         float* dst = meldb + (it.row0 + it.f0) * kAcMel;
         for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];

@@ -79,7 +79,7 @@ template <typename T> struct FbankKernel {
   BatchDesc d;
   float* out;              // [rows][80] raw log-mel lands at its final position
   double* partials;        // [ntiles][80][2]  (sum, sum of squares) per mel bin
-  const T* window;         // [400]  povey * 32768 / 2
+  const T* window;         // [16][26] role-major: povey[16 n1 + role] * 32768 / 2
   const T* tw512;          // [16][16][2]
   float log_floor;         // float32(log(float64(mel_floor)))
 
@@ -162,18 +162,21 @@ template <typename T> struct FbankKernel {
           }
         }
         if (tid < kGroups16) {
-          double s0 = 0.0, s1 = 0.0;
+          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
           const float* g = raw + tid * 16;
           if (tid * 16 + 16 <= it.count) {
+            // four 128-bit loads; the starting quad rotates with tid/2 so the 8 lanes of a
+            // quarter-warp hit 8 different 16-byte bank groups (no conflicts)
+            const float4* g4 = reinterpret_cast<const float4*>(g);
 #pragma unroll
-            for (int j = 0; j < 16; j += 2) {    // rotated start: 2-way instead of 16-way bank conflicts
-              s0 += (double)g[(j + tid) & 15];
-              s1 += (double)g[(j + 1 + tid) & 15];
+            for (int q = 0; q < 4; ++q) {
+              const float4 v = g4[(q + (tid >> 1)) & 3];
+              s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
             }
           } else {
             for (int j = 0; j < 16; ++j) s0 += (tid * 16 + j < it.count) ? (double)g[j] : 0.0;
           }
-          sum16[tid] = s0 + s1;
+          sum16[tid] = (s0 + s1) + (s2 + s3);
         }
       } break;
       case 2: {   // DC term of every frame: c = (1 - 0.97) * mean(frame)
@@ -188,11 +191,8 @@ template <typename T> struct FbankKernel {
       case 3: {   // DC removal + window + stage 1 of the real FFT
         const T c = sc[f];
         T r[25];
-#pragma unroll
-        for (int n1 = 0; n1 < 25; ++n1) {
-          const int n = 16 * n1 + role;
-          r[n1] = ldg(window + n) * (dbuf[phys_idx(kHop * f + n)] - c);
-        }
+        const T* col = dbuf + (kHop + kHop / 32) * f + role;      // phys_idx(160 f + 16 n1 + role) = 165 f + role + 16 n1 + (n1 >> 1)
+        windowed_column<T>(window + role * kWinRow, r, [col, c](int n1) { return col[16 * n1 + (n1 >> 1)] - c; });
         rfft512_stage1<T>(r, role, f, tw512, ex);
       } break;
       case 4:

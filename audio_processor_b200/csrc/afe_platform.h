@@ -31,6 +31,7 @@
 #define AFE_RESTRICT __restrict__
 typedef void* cudaStream_t;
 struct alignas(8) float2 { float x, y; };
+struct alignas(16) double2 { double x, y; };
 struct alignas(16) float4 { float x, y, z, w; };
 struct alignas(8) short4 { short x, y, z, w; };
 #endif
@@ -93,6 +94,24 @@ AFE_HD const float* ldg(const float* const* p) {
 #else
   return *p;
 #endif
+}
+
+// two adjacent table entries (16-byte aligned for double, 8-byte for float) in ONE load
+AFE_HD void ldg2(const double* p, double& a, double& b) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  const double2 v = __ldg(reinterpret_cast<const double2*>(p));
+#else
+  const double2 v = *reinterpret_cast<const double2*>(p);
+#endif
+  a = v.x; b = v.y;
+}
+AFE_HD void ldg2(const float* p, float& a, float& b) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  const float2 v = __ldg(reinterpret_cast<const float2*>(p));
+#else
+  const float2 v = *reinterpret_cast<const float2*>(p);
+#endif
+  a = v.x; b = v.y;
 }
 
 // kernels without per-item context

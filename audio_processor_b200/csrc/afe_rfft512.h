@@ -38,6 +38,19 @@ template <typename T> struct W32 {   // e^{-2 pi i k/32} = c(k) - i s(k), k = 0.
 
 constexpr int kTileFrames = 32;
 constexpr int kRoles = 16;
+constexpr int kWinRow = 26;          // window tables are role-major: w[role][n1] = window[16 n1 + role], 25 used
+
+// the 25 windowed samples of (role, frame): table entries fetched two per load
+template <typename T, class Sample>
+AFE_HD void windowed_column(const T* AFE_RESTRICT wrow, T (&r)[25], Sample sample) {
+#pragma unroll
+  for (int n1 = 0; n1 < 24; n1 += 2) {
+    T w0, w1;
+    ldg2(wrow + n1, w0, w1);
+    r[n1] = w0 * sample(n1); r[n1 + 1] = w1 * sample(n1 + 1);
+  }
+  r[24] = ldg(wrow + 24) * sample(24);
+}
 
 template <typename T>
 AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRICT tw512,
@@ -67,13 +80,27 @@ AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRIC
   ex[(0 * 16 + n2) * kTileFrames + f] = cplx<T>{r0, r16};
 #pragma unroll
   for (int k1 = 1; k1 < 16; ++k1) {
-    const T c = ldg(tw512 + (n2 * 16 + k1) * 2), s = ldg(tw512 + (n2 * 16 + k1) * 2 + 1);   // c + i s
+    T c, s;                                                                                   // c + i s
+    ldg2(tw512 + (n2 * 16 + k1) * 2, c, s);
     ex[(k1 * 16 + n2) * kTileFrames + f] = cplx<T>{re[k1] * c - im[k1] * s, re[k1] * s + im[k1] * c};
   }
 }
 
-template <typename T>
-AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, float* AFE_RESTRICT sP) {
+AFE_HD float rfft_mag(float p) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p));
+  return r;
+#else
+  return std::sqrt(p);
+#endif
+}
+
+// kMag: also store the magnitude sqrt(power) to sM (same layout as sP)
+template <typename T, bool kMag = false>
+AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, float* AFE_RESTRICT sP,
+                           float* AFE_RESTRICT sM = nullptr) {
+#define AFE_PUT(bin, val) { const float p_ = (float)(val); sP[(bin) * kTileFrames + f] = p_; if (kMag) sM[(bin) * kTileFrames + f] = rfft_mag(p_); }
   if (role != 0) {
     T re[16], im[16];
 #pragma unroll
@@ -85,7 +112,7 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
 #pragma unroll
     for (int k2 = 0; k2 < 16; ++k2) {
       const int bin = (k2 < 8) ? (role + 32 * k2) : ((32 - role) + 32 * (15 - k2));
-      sP[bin * kTileFrames + f] = (float)(re[k2] * re[k2] + im[k2] * im[k2]);
+      AFE_PUT(bin, re[k2] * re[k2] + im[k2] * im[k2])
     }
     return;
   }
@@ -102,9 +129,9 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
     for (int m = 0; m < 8; ++m) { re[m] = a0[2 * m]; im[m] = a0[2 * m + 1]; }
     fft8(re, im);
     const T x0 = re[0] + im[0], x8 = re[0] - im[0];
-    sP[(32 * 0) * kTileFrames + f] = (float)(x0 * x0);
-    sP[(32 * 8) * kTileFrames + f] = (float)(x8 * x8);
-    sP[(32 * 4) * kTileFrames + f] = (float)(re[4] * re[4] + im[4] * im[4]);
+    AFE_PUT((32 * 0), x0 * x0)
+    AFE_PUT((32 * 8), x8 * x8)
+    AFE_PUT((32 * 4), re[4] * re[4] + im[4] * im[4])
 #pragma unroll
     for (int k = 1; k < 4; ++k) {
       const int m = 8 - k;
@@ -114,8 +141,8 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
       const T c = W16<T>::c(k), s = W16<T>::s(k);
       const T tr = orr * c + oi * s, ti = oi * c - orr * s;
       const T ar = er + tr, ai = ei + ti, br = er - tr, bi = ei - ti;
-      sP[(32 * k) * kTileFrames + f] = (float)(ar * ar + ai * ai);
-      sP[(32 * m) * kTileFrames + f] = (float)(br * br + bi * bi);
+      AFE_PUT((32 * k), ar * ar + ai * ai)
+      AFE_PUT((32 * m), br * br + bi * bi)
     }
   }
   {
@@ -130,9 +157,10 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int m = (k & 1) ? (15 - k) / 2 : k / 2;
-      sP[(16 + 32 * k) * kTileFrames + f] = (float)(re[m] * re[m] + im[m] * im[m]);
+      AFE_PUT((16 + 32 * k), re[m] * re[m] + im[m] * im[m])
     }
   }
 }
+#undef AFE_PUT
 
 }  // namespace afe

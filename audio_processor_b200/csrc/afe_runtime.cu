@@ -226,9 +226,13 @@ int afe_create(int device, afe_ctx** out) {
 #endif
   bool ok = true;
   {
+    // window tables are role-major for the FFT's stage 1: t[role][n1] = w[16 n1 + role] (afe_rfft512.h)
     std::vector<double> w = make_povey_window();
-    std::vector<double> w64(w.size()); std::vector<float> w32(w.size());
-    for (size_t i = 0; i < w.size(); ++i) { w64[i] = w[i] * 16384.0; w32[i] = (float)(w[i] * 16384.0); }   // 32768 / 2
+    std::vector<double> w64(16 * 26, 0.0); std::vector<float> w32(16 * 26, 0.f);
+    for (size_t i = 0; i < w.size(); ++i) {
+      const size_t j = (i % 16) * 26 + i / 16;
+      w64[j] = w[i] * 16384.0; w32[j] = (float)(w[i] * 16384.0);                                          // 32768 / 2
+    }
     ok = ok && (c->d_povey64 = c->upload(w64)) && (c->d_povey32 = c->upload(w32));
     std::vector<double> tw = make_twiddle512();
     std::vector<float> tw32(tw.begin(), tw.end());
@@ -240,8 +244,8 @@ int afe_create(int device, afe_ctx** out) {
          (c->kaldi_mel_dev.iv_start = c->upload(mel.iv_start)) && (c->kaldi_mel_dev.iv_count = c->upload(mel.iv_count)) &&
          (c->kaldi_mel_dev.role_iv = c->upload(mel.role_iv));
     std::vector<double> hn = make_hann_periodic();
-    std::vector<float> hn32(hn.size());
-    for (size_t i = 0; i < hn.size(); ++i) hn32[i] = (float)(hn[i] * 0.5);
+    std::vector<float> hn32(16 * 26, 0.f);
+    for (size_t i = 0; i < hn.size(); ++i) hn32[(i % 16) * 26 + i / 16] = (float)(hn[i] * 0.5);
     ok = ok && (c->d_hann32 = c->upload(hn32));
     SparseBank htk = make_htk_mel_bank();
     ok = ok && (c->d_htk_start = c->upload(htk.start)) && (c->d_htk_count = c->upload(htk.count)) &&
