@@ -215,23 +215,25 @@ struct AcousticTileKernel {
         double e = 0.0, c = 0.0, c2 = 0.0, kd = (double)kb;
         float fx = 0.f;
         const bool has_next = (f + 1 < it.nvalid);
+        // first / last valid frame: their magnitudes are the tile's boundary spectra
+        float* bd = (f == 0) ? boundary + it.item * 2 * kBoundary
+                             : (f == it.nvalid - 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
+        float* bd2 = (f == 0 && it.nvalid == 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
+#define AFE_AC_BIN(j) {                                                            \
+            const float m = sM[(kb + (j)) * kTileFrames + f];                          \
+            const double md = (double)m, t = md * kd;                                  \
+            e += md; c += t; c2 += t * kd; kd += 1.0;                                  \
+            if (has_next) fx += tmax(sM[(kb + (j)) * kTileFrames + f + 1] - m, 0.f);   \
+            if (bd) bd[kb + (j)] = m;                                                  \
+            if (bd2) bd2[kb + (j)] = m; }
         if (role < 15) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float m = sM[(kb + j) * kTileFrames + f];
-            const double md = (double)m, t = md * kd;
-            e += md; c += t; c2 += t * kd; kd += 1.0;
-            if (has_next) fx += tmax(sM[(kb + j) * kTileFrames + f + 1] - m, 0.f);
-          }
+          for (int j = 0; j < 16; ++j) AFE_AC_BIN(j)
         } else {
 #pragma unroll
-          for (int j = 0; j < 17; ++j) {
-            const float m = sM[(kb + j) * kTileFrames + f];
-            const double md = (double)m, t = md * kd;
-            e += md; c += t; c2 += t * kd; kd += 1.0;
-            if (has_next) fx += tmax(sM[(kb + j) * kTileFrames + f + 1] - m, 0.f);
-          }
+          for (int j = 0; j < 17; ++j) AFE_AC_BIN(j)
         }
+#undef AFE_AC_BIN
         part[0 * 512 + tid] = e; part[1 * 512 + tid] = c; part[2 * 512 + tid] = c2; fxp[tid] = fx;
       } break;
       case 5: {   // per-frame scalars: warp 0 spectral totals, warp 1 rms / zcr, warp 2 max dB
@@ -277,12 +279,22 @@ struct AcousticTileKernel {
         if (role == 15 && hi_below) {
           pf[2 * 32 + f] = 0.f;                             // no bin reaches the threshold: argmax of all-False is 0
         } else if (lo_below && !hi_below) {
+          // cum is monotone, so the number of bins below the threshold is a plain count:
+          // straight-line code, the only dependent chain is the 16 additions
           double acc = lo;
           int below = 0;
-          for (int k = kb; k < ke; ++k) {
-            acc += (double)sM[k * kTileFrames + f];
-            if (!((float)acc < thr)) break;
-            ++below;
+          if (role < 15) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              acc += (double)sM[(kb + j) * kTileFrames + f];
+              below += ((float)acc < thr) ? 1 : 0;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 17; ++j) {
+              acc += (double)sM[(kb + j) * kTileFrames + f];
+              below += ((float)acc < thr) ? 1 : 0;
+            }
           }
           pf[2 * 32 + f] = 31.25f * (float)(kb + below);
         }
@@ -308,12 +320,6 @@ struct AcousticTileKernel {
           float mx = -3.0e38f;
           for (int j = 0; j < it.nvalid; ++j) mx = tmax(mx, pf[6 * 32 + j]);
           rec[13] = (double)mx;
-        }
-        if (tid >= 128 && tid < 128 + kBins) {
-          const int k = tid - 128;
-          float* bd = boundary + it.item * 2 * kBoundary;
-          bd[k] = sM[k * kTileFrames + 0];
-          bd[kBoundary + k] = sM[k * kTileFrames + (it.nvalid - 1)];
         }
         float* dst = meldb + (it.row0 + it.f0) * kAcMel;
         for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];

@@ -31,7 +31,7 @@ FBANK_BYTES_PER_FRAME = 962.0          # 640 B new samples + 320 B
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="afe", choices=["afe", "reference"])
     ap.add_argument("--calls", type=int, default=64, help="calls per GPU per step")

@@ -7,7 +7,7 @@ O=gpurun_out/$TAG
 mkdir -p $O
 python -m pytest tests -m gpu -x -q > $O/gpu_tests.log 2>&1; echo "pytest exit $?" >> $O/gpu_tests.log
 tail -3 $O/gpu_tests.log
-python bench.py --steps 5 --warmup 3 > $O/bench_line.json 2> $O/bench.err; echo "bench exit $?"
+python bench.py --steps 20 --warmup 3 > $O/bench_line.json 2> $O/bench.err; echo "bench exit $?"
 cat $O/bench_line.json
 python tools/microbench.py > $O/microbench.json 2> $O/microbench.err; echo "microbench exit $?"
 cat $O/microbench.json
