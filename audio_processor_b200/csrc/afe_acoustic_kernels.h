@@ -212,7 +212,9 @@ struct AcousticTileKernel {
           mx = tmax(mx, db);
         });
         red[tid] = mx;
-        double e = 0.0, c = 0.0, c2 = 0.0, kd = (double)kb;
+        // moments over k = kb + j with the LOCAL index j as float64 immediates (small integers fit
+        // the 32-bit immediate form): 4 FP64 operations per bin, shifted to k once per thread
+        double e = 0.0, c = 0.0, c2 = 0.0;
         float fx = 0.f;
         const bool has_next = (f + 1 < it.nvalid);
         // first / last valid frame: their magnitudes are the tile's boundary spectra
@@ -221,8 +223,8 @@ struct AcousticTileKernel {
         float* bd2 = (f == 0 && it.nvalid == 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
 #define AFE_AC_BIN(j) {                                                            \
             const float m = sM[(kb + (j)) * kTileFrames + f];                          \
-            const double md = (double)m, t = md * kd;                                  \
-            e += md; c += t; c2 += t * kd; kd += 1.0;                                  \
+            const double md = (double)m;                                               \
+            e += md; c += md * (double)(j); c2 += md * (double)((j) * (j));            \
             if (has_next) fx += tmax(sM[(kb + (j)) * kTileFrames + f + 1] - m, 0.f);   \
             if (bd) bd[kb + (j)] = m;                                                  \
             if (bd2) bd2[kb + (j)] = m; }
@@ -234,6 +236,11 @@ struct AcousticTileKernel {
           for (int j = 0; j < 17; ++j) AFE_AC_BIN(j)
         }
 #undef AFE_AC_BIN
+        {   // sum m k = kb e + c ; sum m k^2 = kb^2 e + 2 kb c + c2   (all exact products)
+          const double kd = (double)kb;
+          c2 = c2 + kd * (2.0 * c + kd * e);
+          c = c + kd * e;
+        }
         part[0 * 512 + tid] = e; part[1 * 512 + tid] = c; part[2 * 512 + tid] = c2; fxp[tid] = fx;
       } break;
       case 5: {   // per-frame scalars: warp 0 spectral totals, warp 1 rms / zcr, warp 2 max dB

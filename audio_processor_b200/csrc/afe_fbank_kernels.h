@@ -55,8 +55,8 @@ template <typename T> struct FbankSmem {
   static constexpr size_t kRawBytes = sizeof(float) * kTileSamples;                 // 21440 per staging buffer
   static constexpr size_t kRawOff = 0;                                              // float[2][5360]
   static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double psum[5][32] (+ spare)
-  static constexpr size_t kCOff = kSumOff + sizeof(double) * 336;
-  static constexpr size_t kDOff = kCOff + sizeof(double) * 32;                      // T[5528] | sP + sOut
+  static constexpr size_t kPsumOff = kSumOff + sizeof(double) * 336;
+  static constexpr size_t kDOff = kPsumOff + sizeof(double) * 160;                  // T[5528] | sP + sOut
   static constexpr size_t kDBytesT = sizeof(T) * (kTileSamples + kTileSamples / 32 + 8);
   static constexpr size_t kPBytes = sizeof(float) * (kBins * kTileFrames);          // 32896
   static constexpr size_t kOutBytes = sizeof(float) * (kTileFrames * kOutStride);   // 10368
@@ -69,7 +69,7 @@ template <typename T> struct FbankSmem {
 template <typename T> struct FbankKernel {
   static constexpr int kThreads = kRoles * kTileFrames;   // 512
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 6;
+  static constexpr int kPhases = 7;
   static constexpr bool kAsyncStage = true;
   static constexpr size_t kStageOff = FbankSmem<T>::kRawOff;
   static constexpr size_t kStageBytes = FbankSmem<T>::kRawBytes;
@@ -127,7 +127,8 @@ template <typename T> struct FbankKernel {
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     using S = FbankSmem<T>;
     float* raw = reinterpret_cast<float*>(smem + S::kRawOff + (size_t)it.buf * S::kRawBytes);
-    double* psum = reinterpret_cast<double*>(smem + S::kSumOff);     // [5][32] partial frame sums
+    double* sum16 = reinterpret_cast<double*>(smem + S::kSumOff);    // [335] sums of 16 samples
+    double* psum = reinterpret_cast<double*>(smem + S::kPsumOff);    // [5][32] sums of 80 samples (5 per frame)
     T* dbuf = reinterpret_cast<T*>(smem + S::kDOff);
     float* sP = reinterpret_cast<float*>(smem + S::kDOff);
     float* sOut = reinterpret_cast<float*>(smem + S::kDOff + S::kPBytes);
@@ -138,48 +139,53 @@ template <typename T> struct FbankKernel {
       case 0: {   // cooperative staging (the CUDA driver replaces it by a TMA bulk copy when it can)
         for (int i = tid; i < it.count; i += kThreads) raw[i] = it.src[i];
       } break;
-      case 1: {   // warps 0-10: pre-emphasis in T into the padded layout; warps 11-15: frame sums
-        constexpr int kPre = 352;                // 11 warps
-        if (tid < kPre) {
-          // element i = tid + 352 j sits at i + (i >> 5) = tid + role + 363 j
-          if (it.count == kTileSamples) {        // full tile: no bounds checks
-            T* dp = dbuf + tid + role;
-            const float* rp = raw + tid;
+      case 1: {   // pre-emphasis in T into the padded layout + 16-sample partial sums
+        // element i = tid + 512 j sits at i + (i >> 5) = tid + role + 528 j
+        if (it.count == kTileSamples) {          // full tile: no bounds checks
+          T* dp = dbuf + tid + role;
+          const float* rp = raw + tid;
 #pragma unroll
-            for (int j = 0; j < kTileSamples / kPre; ++j) {
-              const T x = (T)rp[kPre * j];
-              const T xm = (j == 0 && tid == 0) ? T(0) : (T)rp[kPre * j - 1];
-              dp[(kPre + 11) * j] = x - T(0.97) * xm;
-            }
-            if (tid < kTileSamples % kPre) {
-              constexpr int j = kTileSamples / kPre;
-              dp[(kPre + 11) * j] = (T)rp[kPre * j] - T(0.97) * (T)rp[kPre * j - 1];
-            }
-          } else {
-            for (int i = tid; i < kTileSamples; i += kPre) {
-              const T x = (i < it.count) ? (T)raw[i] : T(0);
-              const T xm = (i > 0 && i - 1 < it.count) ? (T)raw[i - 1] : T(0);
-              dbuf[phys_idx(i)] = x - T(0.97) * xm;
-            }
+          for (int j = 0; j < kTileSamples / kThreads; ++j) {
+            const T x = (T)rp[kThreads * j];
+            const T xm = (j == 0 && tid == 0) ? T(0) : (T)rp[kThreads * j - 1];
+            dp[(kThreads + 16) * j] = x - T(0.97) * xm;
+          }
+          if (tid < kTileSamples % kThreads) {
+            constexpr int j = kTileSamples / kThreads;
+            dp[(kThreads + 16) * j] = (T)rp[kThreads * j] - T(0.97) * (T)rp[kThreads * j - 1];
           }
         } else {
-          // thread (q, f): float64 sum of samples [80 q, 80 q + 80) of frame f (frame = 5 such
-          // runs).  20 128-bit loads; the starting quad rotates with f, which spreads the 8
-          // lanes of a quarter-warp over all bank groups (frames are 160 words apart).
-          // Frames past nvalid read stale but in-bounds staging words; nobody uses their sums.
-          const int q = role - 11;
-          const float4* g4 = reinterpret_cast<const float4*>(raw + kHop * f + 80 * q);
-          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-#pragma unroll
-          for (int j = 0; j < 20; ++j) {
-            int jj = j + f; jj = (jj >= 40) ? jj - 40 : (jj >= 20) ? jj - 20 : jj;
-            const float4 v = g4[jj];
-            s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
+          for (int i = tid; i < kTileSamples; i += kThreads) {
+            const T x = (i < it.count) ? (T)raw[i] : T(0);
+            const T xm = (i > 0 && i - 1 < it.count) ? (T)raw[i - 1] : T(0);
+            dbuf[phys_idx(i)] = x - T(0.97) * xm;
           }
-          psum[q * kTileFrames + f] = (s0 + s1) + (s2 + s3);
+        }
+        if (tid < kGroups16) {
+          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+          const float* g = raw + tid * 16;
+          if (tid * 16 + 16 <= it.count) {
+            // four 128-bit loads; the starting quad rotates with tid/2 so the 8 lanes of a
+            // quarter-warp hit 8 different 16-byte bank groups (no conflicts)
+            const float4* g4 = reinterpret_cast<const float4*>(g);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float4 v = g4[(q + (tid >> 1)) & 3];
+              s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
+            }
+          } else {
+            for (int j = 0; j < 16; ++j) s0 += (tid * 16 + j < it.count) ? (double)g[j] : 0.0;
+          }
+          sum16[tid] = (s0 + s1) + (s2 + s3);
         }
       } break;
-      case 2: {   // DC removal + window + stage 1 of the real FFT
+      case 2: {   // second level of the frame sums: thread (q, f) adds groups 10 f + 5 q .. + 4  (5 warps)
+        if (tid < 5 * kTileFrames) {
+          const double* g = sum16 + 10 * f + 5 * role;
+          psum[role * kTileFrames + f] = ((g[0] + g[1]) + (g[2] + g[3])) + g[4];
+        }
+      } break;
+      case 3: {   // DC removal + window + stage 1 of the real FFT
         const double tot = ((psum[f] + psum[32 + f]) + (psum[64 + f] + psum[96 + f])) + psum[128 + f];
         const T c = (T)((1.0 - 0.97) * (tot * (1.0 / (double)kFrame)));      // (1 - 0.97) * mean(frame)
         T r[25];
@@ -187,17 +193,17 @@ template <typename T> struct FbankKernel {
         windowed_column<T>(window + role * kWinRow, r, [col, c](int n1) { return col[16 * n1 + (n1 >> 1)] - c; });
         rfft512_stage1<T>(r, role, f, tw512, ex);
       } break;
-      case 3:
+      case 4:
         rfft512_stage2<T>(role, f, ex, sP);
         break;
-      case 4: {   // triangular mel bank (generated straight-line code) + floor + log
+      case 5: {   // triangular mel bank (generated straight-line code) + floor + log
         float* row = sOut + f * kOutStride;
         const float lf = log_floor;
         mel_filters_kaldi(role, f, sP, [row, lf](int m, float acc) {
           row[m] = (acc <= kMelFloor) ? lf : fast_log(acc);
         });
       } break;
-      case 5: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
+      case 6: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
         if (tid < kMel) {
           double s[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, q[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
           if (it.nvalid == kTileFrames) {
