@@ -78,6 +78,7 @@ struct AcousticTileKernel {
   static constexpr int kThreads = 512;
   static constexpr int kMinBlocks = 1;
   static constexpr int kPhases = 8;
+  static constexpr int kTailPhases = 0;
   static constexpr bool kAsyncStage = true;
   static constexpr size_t kStageOff = AcSmem::kRawOff;
   static constexpr size_t kStageBytes = AcSmem::kRawBytes;

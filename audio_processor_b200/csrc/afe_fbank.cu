@@ -16,7 +16,8 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 struct FbankLayout {
   int B = 0;
   long ntiles = 0;
-  size_t off_wave = 0, off_len = 0, off_frames = 0, off_prefix = 0, off_row = 0, off_tp = 0, desc_bytes = 0;
+  size_t off_wave = 0, off_len = 0, off_frames = 0, off_prefix = 0, off_row = 0, off_tp = 0, off_whole = 0, off_sel = 0,
+         desc_bytes = 0;
   size_t off_partials = 0, off_stats = 0, total = 0;
 };
 
@@ -34,6 +35,8 @@ FbankLayout fbank_layout(const int64_t* lengths, int B) {
   l.off_row = o;    o = align_up(o + sizeof(int64_t) * (size_t)B, 16);
   l.off_frames = o; o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
   l.off_tp = o;     o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
+  l.off_whole = o;  o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
+  l.off_sel = o;    o = align_up(o + sizeof(int32_t) * (size_t)B, 16);
   l.desc_bytes = o;
   l.off_partials = align_up(o, 256);
   l.off_stats = align_up(l.off_partials + sizeof(double) * 2 * kMel * (size_t)l.ntiles, 256);
@@ -43,9 +46,10 @@ FbankLayout fbank_layout(const int64_t* lengths, int B) {
 
 template <typename T>
 int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, double* partials,
-              const T* window, const T* tw) {
+              const T* window, const T* tw, int32_t* mask, float padding_value) {
   FbankKernel<T> k;
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
+  k.mask = mask; k.padding_value = padding_value;
   k.log_floor = ctx->log_floor;
   ProfScope ps(ctx, AFE_K_FBANK, s);
   return afe_launch(k, FbankSmem<T>::kBytes, ctx->num_sms, s);
@@ -96,6 +100,15 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
   int64_t* hr = reinterpret_cast<int64_t*>(h + l.off_row);
   int32_t* hf = reinterpret_cast<int32_t*>(h + l.off_frames);
   int32_t* ht = reinterpret_cast<int32_t*>(h + l.off_tp);
+  int32_t* hwh = reinterpret_cast<int32_t*>(h + l.off_whole);
+  int32_t* hsel = reinterpret_cast<int32_t*>(h + l.off_sel);
+  // The fbank launch gives block i the tiles [i*per, (i+1)*per).  An utterance whose tiles all fall
+  // into one block is normalised by that block right after its last tile (its raw rows are still
+  // in L2); the others -- at most one per block boundary -- and those without frames go to the
+  // stats / norm kernels.
+  const long grid = afe_async_grid(l.ntiles, ctx->num_sms);
+  const long per = grid > 0 ? (l.ntiles + grid - 1) / grid : 1;
+  int nsel = 0;
   int64_t acc = 0, rows = 0, tp_max = 0;
   bool bad = false;
   for (int b = 0; b < batch; ++b) {
@@ -103,9 +116,12 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
     const int64_t tp = tp_of[b];
     if (T > 0 && !h_waves[b]) bad = true;
     if (tp < T || (tp & 1) || rows_of[b] < 0 || (rows_of[b] & 1)) bad = true;
-    tp_max = std::max(tp_max, tp);
     hw[b] = h_waves[b]; hl[b] = h_lengths[b]; hf[b] = (int32_t)T; hp[b] = acc; hr[b] = rows_of[b]; ht[b] = (int32_t)tp;
-    acc += (T + kTileFrames - 1) / kTileFrames;
+    const int64_t nt = (T + kTileFrames - 1) / kTileFrames;
+    const bool whole = !raw_only && nt > 0 && (acc / per) == ((acc + nt - 1) / per);
+    hwh[b] = whole ? 1 : 0;
+    if (!whole) { hsel[nsel++] = b; tp_max = std::max(tp_max, tp); }
+    acc += nt;
     rows += tp;
   }
   hp[batch] = acc;
@@ -125,14 +141,17 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
   d.tile_prefix = reinterpret_cast<const int64_t*>(ws + l.off_prefix);
   d.out_row = reinterpret_cast<const int64_t*>(ws + l.off_row);
   d.tp = reinterpret_cast<const int32_t*>(ws + l.off_tp);
+  d.whole = reinterpret_cast<const int32_t*>(ws + l.off_whole);
+  d.sel = reinterpret_cast<const int32_t*>(ws + l.off_sel);
+  d.nsel = nsel;
   d.B = batch; d.ntiles = l.ntiles;
   double* partials = reinterpret_cast<double*>(ws + l.off_partials);
   float* stats = reinterpret_cast<float*>(ws + l.off_stats);
 
   int rc = (precision == AFE_PRECISION_F64)
-               ? run_fbank<double>(ctx, s, d, d_features, partials, ctx->d_povey64, ctx->d_tw64)
-               : run_fbank<float>(ctx, s, d, d_features, partials, ctx->d_povey32, ctx->d_tw32);
-  if (rc == 0 && !raw_only && rows > 0) {
+               ? run_fbank<double>(ctx, s, d, d_features, partials, ctx->d_povey64, ctx->d_tw64, d_mask, padding_value)
+               : run_fbank<float>(ctx, s, d, d_features, partials, ctx->d_povey32, ctx->d_tw32, d_mask, padding_value);
+  if (rc == 0 && !raw_only && rows > 0 && nsel > 0) {
     FbankStatsKernel sk{d, partials, stats};
     { ProfScope ps(ctx, AFE_K_FBANK_STATS, s); rc = afe_launch(sk, 0, 1 << 20, s); }
     if (rc == 0) {

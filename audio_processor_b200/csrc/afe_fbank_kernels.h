@@ -27,6 +27,10 @@ struct BatchDesc {            // device-resident description of a batch of mono 
   const int64_t* tile_prefix; // [B+1] exclusive prefix of ceil(T_b / 32)
   const int64_t* out_row;     // [B] first frame row of utterance b in the feature buffer
   const int32_t* tp;          // [B] padded frame count of utterance b's group (even)
+  const int32_t* whole;       // [B] 1: all tiles of b belong to one block of the fbank launch, which
+                              //        normalises b itself; 0: FbankStatsKernel / FbankNormKernel do
+  const int32_t* sel;         // [nsel] utterances left to the stats / norm kernels
+  int nsel;
   int B;
   long ntiles;
 };
@@ -51,12 +55,47 @@ struct MelTables {
 
 constexpr int kMelIv = kMel + 1;                  // 81 intervals
 
+// (mean, denominator) of one mel bin from its float64 sum and sum of squares over n frames --
+// numpy's mean / var(ddof=1) / sqrt(var + 1e-7) of feature_extraction_seamless_m4t.py:283-288
+AFE_HD void fbank_mean_den(double s, double ss, int n, float& mean_out, float& den_out) {
+  const double mean = s / (double)n;
+  const double var = (ss - s * mean) / (double)(n - 1);      // ddof = 1; n == 1 -> 0/0 = NaN
+  const float varf = (float)var;
+  mean_out = (float)mean;
+  den_out = std::sqrt(varf + 1e-7f);
+}
+
+// in-place (x - mean) / den over 128-bit words [q0, q1) of one utterance's (tp x 80) plane, right
+// padding with padding_value, stride-2 mask (the ODD frame's bit: mask[j] = (2j+1 < n)).
+// stat = [80][2] (mean, den).  Shared by the fused tail phase and FbankNormKernel.
+AFE_HD void fbank_normalise_plane(float* feat, int32_t* mask, int64_t row0, int tp, int n, const float* stat,
+                                  float padding_value, int tid, int nthreads, int64_t q0, int64_t q1) {
+  constexpr int kQ = kMel / 4;     // 20 words per frame
+  float4* base = reinterpret_cast<float4*>(feat + row0 * kMel);
+  for (int64_t i4 = q0 + tid; i4 < q1; i4 += nthreads) {
+    const int64_t t = i4 / kQ;
+    const int m4 = (int)(i4 - t * kQ);
+    float4 y = float4{padding_value, padding_value, padding_value, padding_value};
+    if (t < n) {
+      const float4 x = ldcg4(base + i4);
+      const float* st = stat + 8 * m4;
+      y.x = (x.x - st[0]) / st[1]; y.y = (x.y - st[2]) / st[3];
+      y.z = (x.z - st[4]) / st[5]; y.w = (x.w - st[6]) / st[7];
+    }
+    base[i4] = y;
+    if (m4 == 0 && (t & 1)) mask[(row0 >> 1) + (t >> 1)] = (t < n) ? 1 : 0;
+  }
+  (void)tp;
+}
+
 template <typename T> struct FbankSmem {
   static constexpr size_t kRawBytes = sizeof(float) * kTileSamples;                 // 21440 per staging buffer
   static constexpr size_t kRawOff = 0;                                              // float[2][5360]
   static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double psum[5][32] (+ spare)
   static constexpr size_t kPsumOff = kSumOff + sizeof(double) * 336;
-  static constexpr size_t kDOff = kPsumOff + sizeof(double) * 160;                  // T[5528] | sP + sOut
+  static constexpr size_t kAccOff = kPsumOff + sizeof(double) * 160;                // double acc[80][2]: running (sum, sum sq)
+  static constexpr size_t kStatOff = kAccOff + sizeof(double) * 160;                // float stat[80][2]: (mean, denominator)
+  static constexpr size_t kDOff = kStatOff + sizeof(float) * 160;                   // T[5528] | sP + sOut
   static constexpr size_t kDBytesT = sizeof(T) * (kTileSamples + kTileSamples / 32 + 8);
   static constexpr size_t kPBytes = sizeof(float) * (kBins * kTileFrames);          // 32896
   static constexpr size_t kOutBytes = sizeof(float) * (kTileFrames * kOutStride);   // 10368
@@ -70,11 +109,13 @@ template <typename T> struct FbankKernel {
   static constexpr int kThreads = kRoles * kTileFrames;   // 512
   static constexpr int kMinBlocks = 1;
   static constexpr int kPhases = 7;
+  static constexpr int kTailPhases = 1;         // normalisation of a waveform this block owns entirely
   static constexpr bool kAsyncStage = true;
   static constexpr size_t kStageOff = FbankSmem<T>::kRawOff;
   static constexpr size_t kStageBytes = FbankSmem<T>::kRawBytes;
 
-  struct Item { long item; int buf; int bulk; int b; int f0; int nfr; int nvalid; int count; const float* src; int64_t out_row; };
+  struct Item { long item; int buf; int bulk; int b; int f0; int nfr; int nvalid; int count; int whole; int tp;
+                const float* src; int64_t out_row; };
 
   BatchDesc d;
   float* out;              // [rows][80] raw log-mel lands at its final position
@@ -82,11 +123,17 @@ template <typename T> struct FbankKernel {
   const T* window;         // [16][26] role-major: povey[16 n1 + role] * 32768 / 2
   const T* tw512;          // [16][16][2]
   float log_floor;         // float32(log(float64(mel_floor)))
+  int32_t* mask;           // [rows/2]   (fused normalisation only)
+  float padding_value;
 
   AFE_HD long num_items() const { return d.ntiles; }
+  // the last tile of a waveform whose tiles all ran in this block: normalise it here
+  AFE_HD bool tail(const Item& it) const { return it.whole != 0 && it.f0 + kTileFrames >= it.nfr; }
 
   AFE_HD void fill(Item& it, int b, int f0) const {
     it.b = b; it.f0 = f0;
+    it.whole = d.whole ? ldg(d.whole + b) : 0;
+    it.tp = ldg(d.tp + b);
     it.nfr = ldg(d.frames + b);
     it.nvalid = tmin(kTileFrames, it.nfr - f0);
     it.count = (it.nvalid - 1) * kHop + kFrame;
@@ -218,8 +265,22 @@ template <typename T> struct FbankKernel {
               s[0] += v; q[0] += v * v;
             }
           }
-          partials[(it.item * kMel + tid) * 2] = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
-          partials[(it.item * kMel + tid) * 2 + 1] = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+          const double ts = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
+          const double tq = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+          if (!it.whole) {
+            partials[(it.item * kMel + tid) * 2] = ts;
+            partials[(it.item * kMel + tid) * 2 + 1] = tq;
+          } else {
+            // same in-order float64 reduction over the tiles as FbankStatsKernel, kept in shared memory
+            double* acc = reinterpret_cast<double*>(smem + S::kAccOff);
+            const double as = (it.f0 == 0) ? 0.0 + ts : acc[2 * tid] + ts;
+            const double aq = (it.f0 == 0) ? 0.0 + tq : acc[2 * tid + 1] + tq;
+            acc[2 * tid] = as; acc[2 * tid + 1] = aq;
+            if (it.f0 + kTileFrames >= it.nfr) {
+              float* stat = reinterpret_cast<float*>(smem + S::kStatOff);
+              fbank_mean_den(as, aq, it.nfr, stat[2 * tid], stat[2 * tid + 1]);
+            }
+          }
         } else if (tid >= 96) {
           // rows are 320 bytes: 20 128-bit words per frame, destination 16-byte aligned
           float4* dst = reinterpret_cast<float4*>(out + (it.out_row + it.f0) * kMel);
@@ -229,6 +290,11 @@ template <typename T> struct FbankKernel {
             dst[i] = float4{sp[0], sp[1], sp[2], sp[3]};
           }
         }
+      } break;
+      case 7: {   // tail: normalise the whole utterance in place (its raw rows are this block's own, L2-hot)
+        const float* stat = reinterpret_cast<const float*>(smem + S::kStatOff);
+        fbank_normalise_plane(out, mask, it.out_row, it.tp, it.nfr, stat, padding_value, tid, kThreads, 0,
+                              (int64_t)it.tp * (kMel / 4));
       } break;
     }
   }
@@ -244,31 +310,26 @@ struct FbankStatsKernel {
   const double* partials;
   float* stats;            // [B][80][2] = (mean, denominator sqrt(var + 1e-7))
   AFE_PLAIN_ITEM
-  AFE_HD long num_items() const { return d.B; }
+  AFE_HD long num_items() const { return d.nsel; }
   AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
-    const long item = it.item;
+    const long item = ldg(d.sel + it.item);
     if (tid >= kMel) return;
     const long t0 = ldg(d.tile_prefix + item), t1 = ldg(d.tile_prefix + item + 1);
     const int T_b = ldg(d.frames + item);
     double s = 0.0, ss = 0.0;
     for (long t = t0; t < t1; ++t) { s += partials[(t * kMel + tid) * 2]; ss += partials[(t * kMel + tid) * 2 + 1]; }
-    const double mean = s / (double)T_b;
-    const double var = (ss - s * mean) / (double)(T_b - 1);      // ddof = 1; T_b == 1 -> 0/0 = NaN
-    const float varf = (float)var;
-    stats[(item * kMel + tid) * 2] = (float)mean;
-    stats[(item * kMel + tid) * 2 + 1] = std::sqrt(varf + 1e-7f);
+    fbank_mean_den(s, ss, T_b, stats[(item * kMel + tid) * 2], stats[(item * kMel + tid) * 2 + 1]);
   }
 };
 
-// in-place normalisation, right padding and the stride-2 attention mask.
-// One item = 2048 consecutive floats of one utterance's (Tp x 80) plane, moved as 128-bit
-// words (4 mel bins of one frame; planes start 16-byte aligned because rows are 320 bytes).
+// in-place normalisation, right padding and the stride-2 attention mask for the utterances the
+// fbank kernel did not finish itself.  One item = 2048 consecutive floats of one utterance's
+// (Tp x 80) plane, moved as 128-bit words (planes start 16-byte aligned: rows are 320 bytes).
 struct FbankNormKernel {
   static constexpr int kThreads = 256;
   static constexpr int kMinBlocks = 4;
   static constexpr int kPhases = 1;
   static constexpr int kItemFloats = 2048;
-  static constexpr int kQuadsPerRow = kMel / 4;   // 20
   BatchDesc d;
   float* feat;             // [rows][80]
   int32_t* mask;           // [rows/2]
@@ -276,33 +337,16 @@ struct FbankNormKernel {
   float padding_value;
   long items_per_utt;      // ceil(max Tp * 80 / 2048)
   AFE_PLAIN_ITEM
-  AFE_HD long num_items() const { return items_per_utt * d.B; }
+  AFE_HD long num_items() const { return items_per_utt * d.nsel; }
   AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
-    const long item = it.item;
-    const int b = (int)(item / items_per_utt);
-    const long chunk = item % items_per_utt;
-    const int T_b = ldg(d.frames + b);
-    const int64_t plane4 = (int64_t)ldg(d.tp + b) * kQuadsPerRow;
-    const int64_t row0 = ldg(d.out_row + b);
-    float4* base = reinterpret_cast<float4*>(feat + row0 * kMel);
-    const float4* st = reinterpret_cast<const float4*>(stats + (int64_t)b * kMel * 2);
-#pragma unroll
-    for (int v = tid; v < kItemFloats / 4; v += kThreads) {
-      const int64_t i4 = chunk * (kItemFloats / 4) + v;
-      if (i4 >= plane4) break;
-      const int64_t t = i4 / kQuadsPerRow;
-      const int m4 = (int)(i4 - t * kQuadsPerRow);
-      float4 y = float4{padding_value, padding_value, padding_value, padding_value};
-      if (t < T_b) {
-        const float4 x = base[i4];
-        const float4 s0 = ldg(st + 2 * m4), s1 = ldg(st + 2 * m4 + 1);   // (mean, den) x 4 bins
-        y.x = (x.x - s0.x) / s0.y; y.y = (x.y - s0.z) / s0.w;
-        y.z = (x.z - s1.x) / s1.y; y.w = (x.w - s1.z) / s1.w;
-      }
-      base[i4] = y;
-      // the stacked mask takes the ODD frame's bit: mask[b][j] = (2j+1 < T_b)
-      if (m4 == 0 && (t & 1)) mask[(row0 >> 1) + (t >> 1)] = (t < T_b) ? 1 : 0;
-    }
+    const int b = ldg(d.sel + (int)(it.item / items_per_utt));
+    const long chunk = it.item % items_per_utt;
+    const int tp = ldg(d.tp + b);
+    const int64_t plane4 = (int64_t)tp * (kMel / 4);
+    const int64_t q0 = chunk * (kItemFloats / 4);
+    if (q0 >= plane4) return;
+    fbank_normalise_plane(feat, mask, ldg(d.out_row + b), tp, ldg(d.frames + b), stats + (int64_t)b * kMel * 2,
+                          padding_value, tid, kThreads, q0, tmin<int64_t>(plane4, q0 + kItemFloats / 4));
   }
 };
 

@@ -96,6 +96,15 @@ AFE_HD const float* ldg(const float* const* p) {
 #endif
 }
 
+// L2-coherent 128-bit load (data this block wrote earlier in the same launch)
+AFE_HD float4 ldcg4(const float4* p) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  return __ldcg(p);
+#else
+  return *p;
+#endif
+}
+
 // two adjacent table entries (16-byte aligned for double, 8-byte for float) in ONE load
 AFE_HD void ldg2(const double* p, double& a, double& b) {
 #if AFE_CUDA && defined(__CUDA_ARCH__)
@@ -229,6 +238,15 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
         k.phase(ph, cur, afe_smem, tid);
         __syncthreads();
       }
+      if constexpr (K::kTailPhases > 0) {     // block-uniform extra phases (e.g. the last tile of a waveform)
+        if (k.tail(cur)) {
+#pragma unroll
+          for (int ph = K::kPhases; ph < K::kPhases + K::kTailPhases; ++ph) {
+            k.phase(ph, cur, afe_smem, tid);
+            __syncthreads();
+          }
+        }
+      }
     }
   } else {
     for (long item = blockIdx.x; item < n; item += gridDim.x) {
@@ -241,6 +259,9 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
     }
   }
 }
+// blocks of an async (contiguous-range) launch over n items; block i owns items [i*per, (i+1)*per),
+// per = ceil(n / grid).  Host code that needs to know the ranges (fused normalisation) calls this too.
+inline long afe_async_grid(long n, int max_blocks) { return n < (long)max_blocks ? n : (long)max_blocks; }
 template <class K>
 int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t stream) {
   const long n = k.num_items();
@@ -261,6 +282,11 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t strea
 // ------------------------------------------------------------------ host emulation driver
 #include <vector>
 namespace afe {
+// emulation: at most 3 "blocks", so ranges are long and next() crosses waveforms
+inline long afe_async_grid(long n, int max_blocks) {
+  long g = n < (long)max_blocks ? n : (long)max_blocks;
+  return g > 3 ? 3 : g;
+}
 template <class K>
 int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
   const long n = k.num_items();
@@ -269,7 +295,7 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
   unsigned char* smem = reinterpret_cast<unsigned char*>(backing.data());
   long grid = n < (long)max_blocks ? n : (long)max_blocks;
   if constexpr (K::kAsyncStage) {
-    if (grid > 3) grid = 3;                              // long ranges: next() crosses waveforms
+    grid = afe_async_grid(n, max_blocks);
     const long per = (n + grid - 1) / grid;              // contiguous ranges, items derived by next()
     for (long block = 0; block < grid; ++block) {
       const long first = block * per, end = first + per < n ? first + per : n;
@@ -280,6 +306,11 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
         ic.bulk = 0;
         for (int ph = 0; ph < K::kPhases; ++ph)
           for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
+        if constexpr (K::kTailPhases > 0) {
+          if (k.tail(ic))
+            for (int ph = K::kPhases; ph < K::kPhases + K::kTailPhases; ++ph)
+              for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
+        }
       }
     }
   } else {

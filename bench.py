@@ -49,18 +49,20 @@ def workload_name(a):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region: the process is
+    started early (it takes a while to print its first line); mark() / stop() bracket the region
+    and only lines that arrived inside it are used (the nearest one if the region was short)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.t0 = index, None, [], None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
@@ -68,14 +70,23 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def mark(self):
+        self.t0 = time.perf_counter()
 
     def stop(self):
+        t1 = time.perf_counter()
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)                      # let the sample that covers the end of the region arrive
         self.proc.terminate()
+        t0 = self.t0 if self.t0 is not None else 0.0
+        inside = [ln for ts, ln in self.lines if t0 <= ts <= t1 + 0.1]
+        if not inside and self.lines:
+            inside = [min(self.lines, key=lambda p: abs(p[0] - t1))[1]]
         sm, mx, reasons = [], [], set()
-        for ln in self.lines:
+        for ln in inside:
             p = [x.strip() for x in ln.split(",")]
             if len(p) < 7:
                 continue
@@ -169,6 +180,8 @@ def run_afe(a):
     audio_hours_per_step = a.calls * a.call_seconds / 3600.0
     sb = a.sub_batch if a.sub_batch > 0 else None
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()                           # early: nvidia-smi needs a moment before its first line
     for _ in range(max(a.warmup, 3)):
         r = cf.process_calls(dev_calls, 8000, acoustic_to_host=False)
     n_chunks = len(r.chunks)
@@ -177,10 +190,9 @@ def run_afe(a):
     torch.cuda.synchronize(dev)
 
     # ---- timed region A: inputs resident in HBM ------------------------------------------
-    sampler = ClockSampler(local_rank)
     fe.profile(True)
     barrier()
-    sampler.start()
+    sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(a.steps):

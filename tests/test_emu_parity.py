@@ -173,3 +173,17 @@ def test_emu_acoustic_golden(golden):
         tol = np.maximum(1e-3, rel * np.abs(ref))
         bad = [(k, got[k], ref[k]) for k in range(38) if ok[k] and abs(got[k] - ref[k]) > tol[k]]
         assert not bad, (name, bad)
+
+
+def test_emu_fbank_fused_and_fallback_normalisation_agree():
+    """An utterance normalised by the fbank kernel itself (all its tiles in one block) and the
+    same utterance finished by the stats / norm kernels (tiles split over blocks) give the same
+    bits: alone, each waveform is split over the emulation's 3 blocks; in the batch most are whole."""
+    rng = np.random.default_rng(77)
+    lens = [400, 5000, 16000, 40000, 33333, 90000, 12345, 70001]
+    waves = [rng.uniform(-0.5, 0.5, n).astype(np.float32) for n in lens]
+    batch = emu_util.fbank_grouped(waves, 1)
+    for w, (fb, mb) in zip(waves, batch):
+        fa, ma = emu_util.fbank_grouped([w], 1)[0]
+        assert np.array_equal(ma, mb)
+        assert np.array_equal(fa.view(np.uint32), fb.view(np.uint32))
