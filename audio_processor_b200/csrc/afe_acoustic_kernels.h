@@ -207,7 +207,7 @@ struct AcousticTileKernel {
       case 4: {   // 128 HTK mel filters -> dB rows; moments / flux of this role's contiguous bins
         float mx = -3.0e38f;
         float* row = sDb + f * kDbStride;
-        mel_filters_htk(role, f, sP, [row, &mx](int m, float acc) {
+        mel_filters_htk<kTileFrames>(role, f, sP, [row, &mx](int m, float acc) {
           const float db = 10.f * fast_log10(tmax(acc, 1e-10f));
           row[m] = db;
           mx = tmax(mx, db);

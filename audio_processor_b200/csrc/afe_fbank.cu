@@ -26,7 +26,7 @@ FbankLayout fbank_layout(const int64_t* lengths, int B) {
   l.B = B;
   for (int b = 0; b < B; ++b) {
     const int64_t T = afe_fbank_num_frames(lengths[b]);
-    l.ntiles += (long)((T + kTileFrames - 1) / kTileFrames);
+    l.ntiles += (long)((T + kFbTile - 1) / kFbTile);
   }
   size_t o = 0;
   l.off_wave = o;   o = align_up(o + sizeof(void*) * (size_t)B, 16);
@@ -52,7 +52,7 @@ int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, dou
   k.mask = mask; k.padding_value = padding_value;
   k.log_floor = ctx->log_floor;
   ProfScope ps(ctx, AFE_K_FBANK, s);
-  return afe_launch(k, FbankSmem<T>::kBytes, ctx->num_sms, s);
+  return afe_launch(k, FbankKernel<T>::S::kBytes, ctx->num_sms * FbankKernel<T>::kMinBlocks, s);
 }
 
 }  // namespace
@@ -106,7 +106,7 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
   // into one block is normalised by that block right after its last tile (its raw rows are still
   // in L2); the others -- at most one per block boundary -- and those without frames go to the
   // stats / norm kernels.
-  const long grid = afe_async_grid(l.ntiles, ctx->num_sms);
+  const long grid = afe_async_grid(l.ntiles, ctx->num_sms * FbankKernel<double>::kMinBlocks);
   const long per = grid > 0 ? (l.ntiles + grid - 1) / grid : 1;
   int nsel = 0;
   int64_t acc = 0, rows = 0, tp_max = 0;
@@ -117,7 +117,7 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
     if (T > 0 && !h_waves[b]) bad = true;
     if (tp < T || (tp & 1) || rows_of[b] < 0 || (rows_of[b] & 1)) bad = true;
     hw[b] = h_waves[b]; hl[b] = h_lengths[b]; hf[b] = (int32_t)T; hp[b] = acc; hr[b] = rows_of[b]; ht[b] = (int32_t)tp;
-    const int64_t nt = (T + kTileFrames - 1) / kTileFrames;
+    const int64_t nt = (T + kFbTile - 1) / kFbTile;
     const bool whole = !raw_only && nt > 0 && (acc / per) == ((acc + nt - 1) / per);
     hwh[b] = whole ? 1 : 0;
     if (!whole) { hsel[nsel++] = b; tp_max = std::max(tp_max, tp); }

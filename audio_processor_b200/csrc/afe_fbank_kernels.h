@@ -4,9 +4,13 @@
 // called through SeamlessM4TFeatureExtractor (feature_extraction_seamless_m4t.py:112-139)
 // from services/audio_processor.py:253-261 and services/speech_segment.py:226-231.
 //
-// One block = 16 roles (warps) x 32 frames (lanes); one work item = a tile of 32 consecutive
-// frames of one utterance (5360 samples).  Linear path (pre-emphasis, DC removal, window,
-// FFT) in T; power / mel / log in float.
+// One block = 16 roles x TF frames; one work item = a tile of TF consecutive frames of one
+// utterance.  TF = kFbTile.  TF = 32: one role per warp, 128 KB float64 exchange buffer, one block
+// per SM.  TF = 16: two roles share a warp (lanes 0-15 / 16-31), 64 KB exchange, two blocks per
+// SM -- measured on B200 (profiles/README.md, v12/v13): the second block hides ~11 % of the FFT
+// phases' stalls but the half-warp roles double the role-specialised mel code, net zero, so
+// TF = 32 stays.  Linear path (pre-emphasis, DC removal, window, FFT) in T; power / mel / log
+// in float.
 #pragma once
 #include "afe_mel_gen.h"
 #include "afe_rfft512.h"
@@ -14,7 +18,8 @@
 
 namespace afe {
 
-constexpr int kTileSamples = (kTileFrames - 1) * kHop + kFrame;     // 5360
+constexpr int kFbTile = 32;                                         // frames per fbank tile
+constexpr int kTileSamples = (kTileFrames - 1) * kHop + kFrame;     // 5360 (acoustic tile, 32 frames)
 constexpr int kGroups16 = kTileSamples / 16;                        // 335 sums of 16 samples
 constexpr int kOutStride = kMel + 1;                                // 81: conflict-free rows
 
@@ -24,7 +29,7 @@ struct BatchDesc {            // device-resident description of a batch of mono 
   const float* const* wave;   // [B] device pointers
   const int64_t* len;         // [B] samples
   const int32_t* frames;      // [B] fbank frames T_b
-  const int64_t* tile_prefix; // [B+1] exclusive prefix of ceil(T_b / 32)
+  const int64_t* tile_prefix; // [B+1] exclusive prefix of ceil(T_b / kFbTile)
   const int64_t* out_row;     // [B] first frame row of utterance b in the feature buffer
   const int32_t* tp;          // [B] padded frame count of utterance b's group (even)
   const int32_t* whole;       // [B] 1: all tiles of b belong to one block of the fbank launch, which
@@ -88,31 +93,41 @@ AFE_HD void fbank_normalise_plane(float* feat, int32_t* mask, int64_t row0, int 
   (void)tp;
 }
 
-template <typename T> struct FbankSmem {
-  static constexpr size_t kRawBytes = sizeof(float) * kTileSamples;                 // 21440 per staging buffer
-  static constexpr size_t kRawOff = 0;                                              // float[2][5360]
-  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double psum[5][32] (+ spare)
-  static constexpr size_t kPsumOff = kSumOff + sizeof(double) * 336;
-  static constexpr size_t kAccOff = kPsumOff + sizeof(double) * 160;                // double acc[80][2]: running (sum, sum sq)
+// shared-memory carve of one fbank block (TF frames per tile)
+template <typename T, int TF> struct FbankSmem {
+  static constexpr int kSamples = (TF - 1) * kHop + kFrame;                         // 2800 (TF 16) / 5360 (TF 32)
+  static constexpr int kG16 = kSamples / 16;                                        // sums of 16 samples
+  static constexpr size_t kRawBytes = sizeof(float) * kSamples;                     // per staging buffer
+  static constexpr size_t kRawOff = 0;                                              // float[2][kSamples]
+  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double sum16[kG16] (+ spare)
+  static constexpr size_t kPsumOff = kSumOff + sizeof(double) * ((kG16 + 2) / 2 * 2);
+  static constexpr size_t kAccOff = kPsumOff + sizeof(double) * 5 * TF;             // double acc[80][2]: running (sum, sum sq)
   static constexpr size_t kStatOff = kAccOff + sizeof(double) * 160;                // float stat[80][2]: (mean, denominator)
-  static constexpr size_t kDOff = kStatOff + sizeof(float) * 160;                   // T[5528] | sP + sOut
-  static constexpr size_t kDBytesT = sizeof(T) * (kTileSamples + kTileSamples / 32 + 8);
-  static constexpr size_t kPBytes = sizeof(float) * (kBins * kTileFrames);          // 32896
-  static constexpr size_t kOutBytes = sizeof(float) * (kTileFrames * kOutStride);   // 10368
+  static constexpr size_t kDOff = kStatOff + sizeof(float) * 160;                   // T[padded tile] | sP + sOut
+  static constexpr size_t kDBytesT = sizeof(T) * (kSamples + kSamples / 32 + 8);
+  static constexpr size_t kPBytes = sizeof(float) * (kBins * TF);
+  static constexpr size_t kOutBytes = sizeof(float) * (TF * kOutStride);
   static constexpr size_t kDBytes = (kDBytesT > kPBytes + kOutBytes ? kDBytesT : kPBytes + kOutBytes);
-  static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*32]
-  static constexpr size_t kExBytesT = sizeof(cplx<T>) * 16 * 16 * kTileFrames;
+  static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*TF]
+  static constexpr size_t kExBytesT = sizeof(cplx<T>) * 16 * 16 * TF;
   static constexpr size_t kBytes = kExOff + kExBytesT;
+  static_assert(kSamples % 16 == 0, "tile samples must split into groups of 16");
 };
 
-template <typename T> struct FbankKernel {
-  static constexpr int kThreads = kRoles * kTileFrames;   // 512
-  static constexpr int kMinBlocks = 1;
+template <typename T, int TF = kFbTile> struct FbankKernel {
+  using S = FbankSmem<T, TF>;
+  static constexpr int kTile = TF;
+  static constexpr int kThreads = kRoles * TF;            // 256 (TF 16)
+  static constexpr int kMinBlocks = (TF <= 16) ? 2 : 1;   // resident blocks per SM the launch is sized for
   static constexpr int kPhases = 7;
   static constexpr int kTailPhases = 1;         // normalisation of a waveform this block owns entirely
   static constexpr bool kAsyncStage = true;
-  static constexpr size_t kStageOff = FbankSmem<T>::kRawOff;
-  static constexpr size_t kStageBytes = FbankSmem<T>::kRawBytes;
+  static constexpr size_t kStageOff = S::kRawOff;
+  static constexpr size_t kStageBytes = S::kRawBytes;
+  static constexpr int kSamples = S::kSamples;
+  static constexpr int kG16 = S::kG16;
+  static constexpr int kStoreFirst = 96;        // threads [96, kThreads) move the tile's rows to global memory
+  static_assert(5 * TF <= kThreads && kG16 <= kThreads && kMel <= kStoreFirst, "phase thread budgets");
 
   struct Item { long item; int buf; int bulk; int b; int f0; int nfr; int nvalid; int count; int whole; int tp;
                 const float* src; int64_t out_row; };
@@ -128,14 +143,14 @@ template <typename T> struct FbankKernel {
 
   AFE_HD long num_items() const { return d.ntiles; }
   // the last tile of a waveform whose tiles all ran in this block: normalise it here
-  AFE_HD bool tail(const Item& it) const { return it.whole != 0 && it.f0 + kTileFrames >= it.nfr; }
+  AFE_HD bool tail(const Item& it) const { return it.whole != 0 && it.f0 + TF >= it.nfr; }
 
   AFE_HD void fill(Item& it, int b, int f0) const {
     it.b = b; it.f0 = f0;
     it.whole = d.whole ? ldg(d.whole + b) : 0;
     it.tp = ldg(d.tp + b);
     it.nfr = ldg(d.frames + b);
-    it.nvalid = tmin(kTileFrames, it.nfr - f0);
+    it.nvalid = tmin(TF, it.nfr - f0);
     it.count = (it.nvalid - 1) * kHop + kFrame;
     it.src = ldg(d.wave + b) + (int64_t)f0 * kHop;
     it.out_row = ldg(d.out_row + b);
@@ -145,7 +160,7 @@ template <typename T> struct FbankKernel {
     int b, t;
     locate_tile(d, item, b, t);
     it.item = item; it.buf = 0; it.bulk = 0;
-    fill(it, b, t * kTileFrames);
+    fill(it, b, t * TF);
     return it;
   }
   // item cur.item + 1: the next tile of the same utterance, else the first tile of the next
@@ -153,11 +168,11 @@ template <typename T> struct FbankKernel {
   AFE_HD Item next(const Item& cur, long item) const {
     Item it = cur;
     it.item = item;
-    if (cur.f0 + kTileFrames < cur.nfr) {
-      it.f0 = cur.f0 + kTileFrames;
-      it.nvalid = tmin(kTileFrames, cur.nfr - it.f0);
+    if (cur.f0 + TF < cur.nfr) {
+      it.f0 = cur.f0 + TF;
+      it.nvalid = tmin(TF, cur.nfr - it.f0);
       it.count = (it.nvalid - 1) * kHop + kFrame;
-      it.src = cur.src + (int64_t)kTileFrames * kHop;
+      it.src = cur.src + (int64_t)TF * kHop;
       return it;
     }
     int b = cur.b + 1;
@@ -172,43 +187,42 @@ template <typename T> struct FbankKernel {
   }
 
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
-    using S = FbankSmem<T>;
     float* raw = reinterpret_cast<float*>(smem + S::kRawOff + (size_t)it.buf * S::kRawBytes);
-    double* sum16 = reinterpret_cast<double*>(smem + S::kSumOff);    // [335] sums of 16 samples
-    double* psum = reinterpret_cast<double*>(smem + S::kPsumOff);    // [5][32] sums of 80 samples (5 per frame)
+    double* sum16 = reinterpret_cast<double*>(smem + S::kSumOff);    // [kG16] sums of 16 samples
+    double* psum = reinterpret_cast<double*>(smem + S::kPsumOff);    // [5][TF] sums of 80 samples (5 per frame)
     T* dbuf = reinterpret_cast<T*>(smem + S::kDOff);
     float* sP = reinterpret_cast<float*>(smem + S::kDOff);
     float* sOut = reinterpret_cast<float*>(smem + S::kDOff + S::kPBytes);
     cplx<T>* ex = reinterpret_cast<cplx<T>*>(smem + S::kExOff);
-    const int role = tid >> 5, f = tid & 31;
+    const int role = tid / TF, f = tid % TF;
 
     switch (ph) {
       case 0: {   // cooperative staging (the CUDA driver replaces it by a TMA bulk copy when it can)
         for (int i = tid; i < it.count; i += kThreads) raw[i] = it.src[i];
       } break;
       case 1: {   // pre-emphasis in T into the padded layout + 16-sample partial sums
-        // element i = tid + 512 j sits at i + (i >> 5) = tid + role + 528 j
-        if (it.count == kTileSamples) {          // full tile: no bounds checks
-          T* dp = dbuf + tid + role;
+        // element i = tid + kThreads j sits at i + (i >> 5) = tid + (tid >> 5) + (kThreads + kThreads / 32) j
+        constexpr int kRowStep = kThreads + kThreads / 32;
+        constexpr int kFull = kSamples / kThreads, kRest = kSamples % kThreads;
+        if (it.count == kSamples) {          // full tile: no bounds checks
+          T* dp = dbuf + tid + (tid >> 5);
           const float* rp = raw + tid;
 #pragma unroll
-          for (int j = 0; j < kTileSamples / kThreads; ++j) {
+          for (int j = 0; j < kFull; ++j) {
             const T x = (T)rp[kThreads * j];
             const T xm = (j == 0 && tid == 0) ? T(0) : (T)rp[kThreads * j - 1];
-            dp[(kThreads + 16) * j] = x - T(0.97) * xm;
+            dp[kRowStep * j] = x - T(0.97) * xm;
           }
-          if (tid < kTileSamples % kThreads) {
-            constexpr int j = kTileSamples / kThreads;
-            dp[(kThreads + 16) * j] = (T)rp[kThreads * j] - T(0.97) * (T)rp[kThreads * j - 1];
-          }
+          if (kRest > 0 && tid < kRest)
+            dp[kRowStep * kFull] = (T)rp[kThreads * kFull] - T(0.97) * (T)rp[kThreads * kFull - 1];
         } else {
-          for (int i = tid; i < kTileSamples; i += kThreads) {
+          for (int i = tid; i < kSamples; i += kThreads) {
             const T x = (i < it.count) ? (T)raw[i] : T(0);
             const T xm = (i > 0 && i - 1 < it.count) ? (T)raw[i - 1] : T(0);
             dbuf[phys_idx(i)] = x - T(0.97) * xm;
           }
         }
-        if (tid < kGroups16) {
+        if (tid < kG16) {
           double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
           const float* g = raw + tid * 16;
           if (tid * 16 + 16 <= it.count) {
@@ -226,36 +240,36 @@ template <typename T> struct FbankKernel {
           sum16[tid] = (s0 + s1) + (s2 + s3);
         }
       } break;
-      case 2: {   // second level of the frame sums: thread (q, f) adds groups 10 f + 5 q .. + 4  (5 warps)
-        if (tid < 5 * kTileFrames) {
+      case 2: {   // second level of the frame sums: thread (q, f) adds groups 10 f + 5 q .. + 4
+        if (tid < 5 * TF) {
           const double* g = sum16 + 10 * f + 5 * role;
-          psum[role * kTileFrames + f] = ((g[0] + g[1]) + (g[2] + g[3])) + g[4];
+          psum[role * TF + f] = ((g[0] + g[1]) + (g[2] + g[3])) + g[4];
         }
       } break;
       case 3: {   // DC removal + window + stage 1 of the real FFT
-        const double tot = ((psum[f] + psum[32 + f]) + (psum[64 + f] + psum[96 + f])) + psum[128 + f];
+        const double tot = ((psum[f] + psum[TF + f]) + (psum[2 * TF + f] + psum[3 * TF + f])) + psum[4 * TF + f];
         const T c = (T)((1.0 - 0.97) * (tot * (1.0 / (double)kFrame)));      // (1 - 0.97) * mean(frame)
         T r[25];
         const T* col = dbuf + (kHop + kHop / 32) * f + role;      // phys_idx(160 f + 16 n1 + role) = 165 f + role + 16 n1 + (n1 >> 1)
         windowed_column<T>(window + role * kWinRow, r, [col, c](int n1) { return col[16 * n1 + (n1 >> 1)] - c; });
-        rfft512_stage1<T>(r, role, f, tw512, ex);
+        rfft512_stage1<T, TF>(r, role, f, tw512, ex);
       } break;
       case 4:
-        rfft512_stage2<T>(role, f, ex, sP);
+        rfft512_stage2<T, false, TF>(role, f, ex, sP);
         break;
       case 5: {   // triangular mel bank (generated straight-line code) + floor + log
         float* row = sOut + f * kOutStride;
         const float lf = log_floor;
-        mel_filters_kaldi(role, f, sP, [row, lf](int m, float acc) {
+        mel_filters_kaldi<TF>(role, f, sP, [row, lf](int m, float acc) {
           row[m] = (acc <= kMelFloor) ? lf : fast_log(acc);
         });
       } break;
       case 6: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
         if (tid < kMel) {
           double s[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, q[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-          if (it.nvalid == kTileFrames) {
+          if (it.nvalid == TF) {
 #pragma unroll
-            for (int j = 0; j < kTileFrames; ++j) {
+            for (int j = 0; j < TF; ++j) {
               const double v = (double)sOut[j * kOutStride + tid];
               s[j & 7] += v; q[j & 7] += v * v;
             }
@@ -276,15 +290,15 @@ template <typename T> struct FbankKernel {
             const double as = (it.f0 == 0) ? 0.0 + ts : acc[2 * tid] + ts;
             const double aq = (it.f0 == 0) ? 0.0 + tq : acc[2 * tid + 1] + tq;
             acc[2 * tid] = as; acc[2 * tid + 1] = aq;
-            if (it.f0 + kTileFrames >= it.nfr) {
+            if (it.f0 + TF >= it.nfr) {
               float* stat = reinterpret_cast<float*>(smem + S::kStatOff);
               fbank_mean_den(as, aq, it.nfr, stat[2 * tid], stat[2 * tid + 1]);
             }
           }
-        } else if (tid >= 96) {
+        } else if (tid >= kStoreFirst) {
           // rows are 320 bytes: 20 128-bit words per frame, destination 16-byte aligned
           float4* dst = reinterpret_cast<float4*>(out + (it.out_row + it.f0) * kMel);
-          for (int i = tid - 96; i < it.nvalid * (kMel / 4); i += kThreads - 96) {
+          for (int i = tid - kStoreFirst; i < it.nvalid * (kMel / 4); i += kThreads - kStoreFirst) {
             const int row = i / (kMel / 4), c4 = i - row * (kMel / 4);
             const float* sp = sOut + row * kOutStride + 4 * c4;
             dst[i] = float4{sp[0], sp[1], sp[2], sp[3]};

@@ -19,6 +19,8 @@
 #include <cstdint>
 #include <cmath>
 #include <cstring>
+#include <cstdio>
+#include <cstdlib>
 
 #if defined(__CUDACC__) && !defined(AFE_EMULATE)
 #define AFE_CUDA 1
@@ -270,6 +272,15 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t strea
   if (smem_bytes > 48 * 1024) {
     const cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     if (e != cudaSuccess) { note_error("cudaFuncSetAttribute(max dynamic smem)", cudaGetErrorString(e)); return -1; }
+    // all of the SM's configurable L1/shared array as shared memory: kernels sized for several resident
+    // blocks per SM (K::kMinBlocks) only get them with the maximum carve-out
+    cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+    static const bool debug = std::getenv("AFE_DEBUG_OCCUPANCY") != nullptr;
+    if (debug) {
+      int nb = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, K::kThreads, smem_bytes);
+      std::fprintf(stderr, "[afe] %s: %d threads, %zu B dynamic smem, %d resident blocks/SM\n", __PRETTY_FUNCTION__, K::kThreads, smem_bytes, nb);
+    }
   }
   long grid = n < (long)max_blocks ? n : (long)max_blocks;
   phased_kernel<K><<<(unsigned)grid, K::kThreads, smem_bytes, stream>>>(k);

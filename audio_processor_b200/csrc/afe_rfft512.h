@@ -11,9 +11,10 @@
 //                         real rows k1 = 0 and k1 = 16 (two 8-point FFTs).
 //
 // The caller pre-scales the frame by 1/2 (folded into the window table) so that the
-// untangling needs no halving.  Exchange layout: cplx<T> ex[(slot*16 + n2)*32 + f], slot 0
+// untangling needs no halving.  Exchange layout: cplx<T> ex[(slot*16 + n2)*TF + f], slot 0
 // holds the real pair (R[0], R[16]), slot k1 holds the twiddled R[k1].
-// Power layout: float sP[bin*32 + f].
+// Power layout: float sP[bin*TF + f].  TF = frames per tile: 32 (one role per warp) or 16 (two
+// roles per warp, lanes 0-15 / 16-31), which halves the exchange buffer.
 #pragma once
 #include "afe_fft.h"
 
@@ -52,7 +53,7 @@ AFE_HD void windowed_column(const T* AFE_RESTRICT wrow, T (&r)[25], Sample sampl
   r[24] = ldg(wrow + 24) * sample(24);
 }
 
-template <typename T>
+template <typename T, int TF = kTileFrames>
 AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRICT tw512,
                            cplx<T>* AFE_RESTRICT ex) {
   T re[16], im[16];
@@ -77,12 +78,12 @@ AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRIC
     re[m] = er - tr; im[m] = -(ei - ti);                     // R[16-k] = conj(E - T)
   }
   re[8] = T(2) * re[8]; im[8] = T(-2) * im[8];               // R[8] = 2 conj(C[8])
-  ex[(0 * 16 + n2) * kTileFrames + f] = cplx<T>{r0, r16};
+  ex[(0 * 16 + n2) * TF + f] = cplx<T>{r0, r16};
 #pragma unroll
   for (int k1 = 1; k1 < 16; ++k1) {
     T c, s;                                                                                   // c + i s
     ldg2(tw512 + (n2 * 16 + k1) * 2, c, s);
-    ex[(k1 * 16 + n2) * kTileFrames + f] = cplx<T>{re[k1] * c - im[k1] * s, re[k1] * s + im[k1] * c};
+    ex[(k1 * 16 + n2) * TF + f] = cplx<T>{re[k1] * c - im[k1] * s, re[k1] * s + im[k1] * c};
   }
 }
 
@@ -97,15 +98,15 @@ AFE_HD float rfft_mag(float p) {
 }
 
 // kMag: also store the magnitude sqrt(power) to sM (same layout as sP)
-template <typename T, bool kMag = false>
+template <typename T, bool kMag = false, int TF = kTileFrames>
 AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, float* AFE_RESTRICT sP,
                            float* AFE_RESTRICT sM = nullptr) {
-#define AFE_PUT(bin, val) { const float p_ = (float)(val); sP[(bin) * kTileFrames + f] = p_; if (kMag) sM[(bin) * kTileFrames + f] = rfft_mag(p_); }
+#define AFE_PUT(bin, val) { const float p_ = (float)(val); sP[(bin) * TF + f] = p_; if (kMag) sM[(bin) * TF + f] = rfft_mag(p_); }
   if (role != 0) {
     T re[16], im[16];
 #pragma unroll
     for (int n2 = 0; n2 < 16; ++n2) {
-      const cplx<T> v = ex[(role * 16 + n2) * kTileFrames + f];
+      const cplx<T> v = ex[(role * 16 + n2) * TF + f];
       re[n2] = v.re; im[n2] = v.im;
     }
     fft16(re, im);
@@ -120,7 +121,7 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
   T a0[16], a16[16];
 #pragma unroll
   for (int n2 = 0; n2 < 16; ++n2) {
-    const cplx<T> v = ex[(0 * 16 + n2) * kTileFrames + f];
+    const cplx<T> v = ex[(0 * 16 + n2) * TF + f];
     a0[n2] = v.re; a16[n2] = v.im;
   }
   {

@@ -37,7 +37,7 @@ static void emit(const SparseBank& b, const char* name) {
   std::vector<int> cuts = partition(cost, 16);
   printf("// %s: %d filters, %d intervals; role costs:", name, F, F + 1);
   for (int r = 0; r < 16; ++r) { int c = 0; for (int i = cuts[r]; i < cuts[r + 1]; ++i) c += cost[i]; printf(" %d", c); }
-  printf("\nAFE_HD void mel_intervals_%s(int role, int f, const float* AFE_RESTRICT sP, float* AFE_RESTRICT sU, float* AFE_RESTRICT sD) {\n", name);
+  printf("\ntemplate <int TF> AFE_HD void mel_intervals_%s(int role, int f, const float* AFE_RESTRICT sP, float* AFE_RESTRICT sU, float* AFE_RESTRICT sD) {\n", name);
   printf("  float u = 0.f, d = 0.f;\n  switch (role) {\n");
   for (int r = 0; r < 16; ++r) {
     printf("    case %d:\n", r);
@@ -71,7 +71,7 @@ static void emit_fused(const SparseBank& b, const char* name) {
   std::vector<int> cuts = partition(cost, 16);
   printf("// %s fused: filters per role:", name);
   for (int r = 0; r < 16; ++r) printf(" %d", cuts[r + 1] - cuts[r]);
-  printf("\ntemplate <class Out> AFE_HD void mel_filters_%s(int role, int f, const float* AFE_RESTRICT sP, Out out) {\n", name);
+  printf("\ntemplate <int TF, class Out> AFE_HD void mel_filters_%s(int role, int f, const float* AFE_RESTRICT sP, Out out) {\n", name);
   printf("  float u = 0.f, d = 0.f, pu = 0.f;\n  switch (role) {\n");
   for (int r = 0; r < 16; ++r) {
     printf("    case %d:\n", r);
@@ -121,18 +121,18 @@ int main() {
   printf("// GENERATED by tools/gen_mel.cc from afe_tables.cc -- do not edit.\n");
   printf("// Interval form of the triangular banks (afe_tables.h): a bin in interval i feeds the up-slope\n");
   printf("// of filter i and the down-slope of filter i-1; filter m = U[m] + D[m+1].  Role r (warp r)\n");
-  printf("// owns a contiguous run of intervals; lanes are frames.  sP[bin*32+f], sU/sD[interval*32+f].\n");
+  printf("// owns a contiguous run of intervals; lanes are frames (TF per tile).  sP[bin*TF+f], sU/sD[interval*TF+f].\n");
   printf("#pragma once\n#include \"afe_platform.h\"\nnamespace afe {\n");
-  printf("#define AFE_MEL_UD(k, wu, wd) { const float p = sP[(k) * 32 + f]; u = fma_f(wu, p, u); d = fma_f(wd, p, d); }\n");
-  printf("#define AFE_MEL_U(k, wu) { u = fma_f(wu, sP[(k) * 32 + f], u); }\n");
-  printf("#define AFE_MEL_D(k, wd) { d = fma_f(wd, sP[(k) * 32 + f], d); }\n");
-  printf("#define AFE_MEL_END(i) { sU[(i) * 32 + f] = u; sD[(i) * 32 + f] = d; u = 0.f; d = 0.f; }\n\n");
+  printf("#define AFE_MEL_UD(k, wu, wd) { const float p = sP[(k) * TF + f]; u = fma_f(wu, p, u); d = fma_f(wd, p, d); }\n");
+  printf("#define AFE_MEL_U(k, wu) { u = fma_f(wu, sP[(k) * TF + f], u); }\n");
+  printf("#define AFE_MEL_D(k, wd) { d = fma_f(wd, sP[(k) * TF + f], d); }\n");
+  printf("#define AFE_MEL_END(i) { sU[(i) * TF + f] = u; sD[(i) * TF + f] = d; u = 0.f; d = 0.f; }\n\n");
   emit(make_kaldi_mel_bank(), "kaldi");
   emit(make_htk_mel_bank(), "htk");
   printf("#undef AFE_MEL_UD\n#undef AFE_MEL_U\n#undef AFE_MEL_D\n#undef AFE_MEL_END\n\n");
-  printf("#define AFE_MEL_UD(k, wu, wd) { const float p = sP[(k) * 32 + f]; u = fma_f(wu, p, u); d = fma_f(wd, p, d); }\n");
-  printf("#define AFE_MEL_U(k, wu) { u = fma_f(wu, sP[(k) * 32 + f], u); }\n");
-  printf("#define AFE_MEL_D(k, wd) { d = fma_f(wd, sP[(k) * 32 + f], d); }\n");
+  printf("#define AFE_MEL_UD(k, wu, wd) { const float p = sP[(k) * TF + f]; u = fma_f(wu, p, u); d = fma_f(wd, p, d); }\n");
+  printf("#define AFE_MEL_U(k, wu) { u = fma_f(wu, sP[(k) * TF + f], u); }\n");
+  printf("#define AFE_MEL_D(k, wd) { d = fma_f(wd, sP[(k) * TF + f], d); }\n");
   printf("#define AFE_MEL_FIRST() { pu = u; u = 0.f; d = 0.f; }\n");
   printf("#define AFE_MEL_OUT(m) { out(m, pu + d); pu = u; u = 0.f; d = 0.f; }\n\n");
   emit_fused(make_kaldi_mel_bank(), "kaldi");
