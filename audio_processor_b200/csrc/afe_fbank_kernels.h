@@ -99,9 +99,9 @@ template <typename T, int TF> struct FbankSmem {
   static constexpr int kG16 = kSamples / 16;                                        // sums of 16 samples
   static constexpr size_t kRawBytes = sizeof(float) * kSamples;                     // per staging buffer
   static constexpr size_t kRawOff = 0;                                              // float[2][kSamples]
-  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double sum16[kG16] (+ spare)
-  static constexpr size_t kPsumOff = kSumOff + sizeof(double) * ((kG16 + 2) / 2 * 2);
-  static constexpr size_t kAccOff = kPsumOff + sizeof(double) * 5 * TF;             // double acc[80][2]: running (sum, sum sq)
+  static constexpr int kG80 = kG16 / 5;                                             // sums of 80 samples: 2 TF + 3
+  static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double psum80[kG80] (+ spare)
+  static constexpr size_t kAccOff = kSumOff + sizeof(double) * ((kG80 + 2) / 2 * 2);   // double acc[80][2]: running (sum, sum sq)
   static constexpr size_t kStatOff = kAccOff + sizeof(double) * 160;                // float stat[80][2]: (mean, denominator)
   static constexpr size_t kDOff = kStatOff + sizeof(float) * 160;                   // T[padded tile] | sP + sOut
   static constexpr size_t kDBytesT = sizeof(T) * (kSamples + kSamples / 32 + 8);
@@ -110,8 +110,10 @@ template <typename T, int TF> struct FbankSmem {
   static constexpr size_t kDBytes = (kDBytesT > kPBytes + kOutBytes ? kDBytesT : kPBytes + kOutBytes);
   static constexpr size_t kExOff = (kDOff + kDBytes + 15) / 16 * 16;                // cplx<T>[16*16*TF]
   static constexpr size_t kExBytesT = sizeof(cplx<T>) * 16 * 16 * TF;
-  static constexpr size_t kBytes = kExOff + kExBytesT;
-  static_assert(kSamples % 16 == 0, "tile samples must split into groups of 16");
+  static constexpr size_t kWinOff = kExOff + kExBytesT;                             // T window[16][26] (block_init)
+  static constexpr size_t kTwOff = kWinOff + sizeof(T) * kRoles * kWinRow;          // T tw512[16][16][2]
+  static constexpr size_t kBytes = kTwOff + sizeof(T) * kRoles * 32;
+  static_assert(kSamples % 80 == 0 && kG80 == 2 * TF + 3, "tile samples must split into groups of 16 and 80");
 };
 
 template <typename T, int TF = kFbTile> struct FbankKernel {
@@ -119,7 +121,7 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   static constexpr int kTile = TF;
   static constexpr int kThreads = kRoles * TF;            // 256 (TF 16)
   static constexpr int kMinBlocks = (TF <= 16) ? 2 : 1;   // resident blocks per SM the launch is sized for
-  static constexpr int kPhases = 7;
+  static constexpr int kPhases = 6;
   static constexpr int kTailPhases = 1;         // normalisation of a waveform this block owns entirely
   static constexpr bool kAsyncStage = true;
   static constexpr size_t kStageOff = S::kRawOff;
@@ -127,7 +129,9 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   static constexpr int kSamples = S::kSamples;
   static constexpr int kG16 = S::kG16;
   static constexpr int kStoreFirst = 96;        // threads [96, kThreads) move the tile's rows to global memory
-  static_assert(5 * TF <= kThreads && kG16 <= kThreads && kMel <= kStoreFirst, "phase thread budgets");
+  static constexpr int kG80 = S::kG80;
+  static constexpr int kPrefetchThread = kThreads - 32;   // lane 0 of the last warp: it has no group in phase 1
+  static_assert((kG16 + 29) / 30 * 32 <= kThreads - 32 && kMel <= kStoreFirst, "phase thread budgets");
 
   struct Item { long item; int buf; int bulk; int b; int f0; int nfr; int nvalid; int count; int whole; int tp;
                 const float* src; int64_t out_row; };
@@ -135,8 +139,8 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   BatchDesc d;
   float* out;              // [rows][80] raw log-mel lands at its final position
   double* partials;        // [ntiles][80][2]  (sum, sum of squares) per mel bin
-  const T* window;         // [16][26] role-major: povey[16 n1 + role] * 32768 / 2
-  const T* tw512;          // [16][16][2]
+  const T* window;         // [16][26] role-major: povey[16 n1 + role] * 32768 / 2   (copied to shared memory
+  const T* tw512;          // [16][16][2]                                            once per block: block_init)
   float log_floor;         // float32(log(float64(mel_floor)))
   int32_t* mask;           // [rows/2]   (fused normalisation only)
   float padding_value;
@@ -144,6 +148,14 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   AFE_HD long num_items() const { return d.ntiles; }
   // the last tile of a waveform whose tiles all ran in this block: normalise it here
   AFE_HD bool tail(const Item& it) const { return it.whole != 0 && it.f0 + TF >= it.nfr; }
+  // once per block, before its first item: the FFT tables move to shared memory (a table read is then a
+  // 23-cycle broadcast load instead of an L1 round trip queued behind the exchange stores)
+  AFE_HD void block_init(unsigned char* smem, int tid) const {
+    T* w = reinterpret_cast<T*>(smem + S::kWinOff);
+    T* t = reinterpret_cast<T*>(smem + S::kTwOff);
+    for (int i = tid; i < kRoles * kWinRow; i += kThreads) w[i] = ldg(window + i);
+    for (int i = tid; i < kRoles * 32; i += kThreads) t[i] = ldg(tw512 + i);
+  }
 
   AFE_HD void fill(Item& it, int b, int f0) const {
     it.b = b; it.f0 = f0;
@@ -186,10 +198,57 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
     return (reinterpret_cast<uintptr_t>(it.src) & 15u) == 0;
   }
 
+  // Samples [16 t, 16 t + 16) of the tile: pre-emphasis x[n] - 0.97 x[n-1] in T into the padded layout
+  // (kStore) and the float64 sum of the 16 raw samples.  The four 128-bit chunks are visited in an
+  // order rotated by rot(t), which makes both the 128-bit loads (8 lanes per wavefront) and the 64-bit
+  // stores (16 lanes per wavefront, element 16 t + j at 16 t + (t >> 1) + j) bank-conflict free, and
+  // every sample is converted to T exactly once.
+  template <bool kStore>
+  AFE_HD static double group16(const float* raw, T* dbuf, int t, int count) {
+    if (16 * t + 16 <= count) {
+      const int rot = ((t >> 1) + 2 * (t & 1)) & 3;
+      const float4* g4 = reinterpret_cast<const float4*>(raw + 16 * t);
+      T x[4][4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 v = g4[(q + rot) & 3];
+        x[q][0] = (T)v.x; x[q][1] = (T)v.y; x[q][2] = (T)v.z; x[q][3] = (T)v.w;
+      }
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { s0 += (double)x[q][0]; s1 += (double)x[q][1]; s2 += (double)x[q][2]; s3 += (double)x[q][3]; }
+      if (kStore) {
+        const T xp = (t > 0) ? (T)raw[16 * t - 1] : T(0);      // the sample before the group (frame sample 0 has window 0)
+        T* dp = dbuf + 16 * t + (t >> 1);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int cq = (q + rot) & 3;                         // chunk held by slot q; slot q-1 holds chunk cq-1
+          const T xm = (cq == 0) ? xp : x[(q + 3) & 3][3];
+          T* o = dp + 4 * cq;
+          o[0] = x[q][0] - T(0.97) * xm;
+          o[1] = x[q][1] - T(0.97) * x[q][0];
+          o[2] = x[q][2] - T(0.97) * x[q][1];
+          o[3] = x[q][3] - T(0.97) * x[q][2];
+        }
+      }
+      return (s0 + s1) + (s2 + s3);
+    }
+    double s = 0.0;
+    for (int j = 0; j < 16; ++j) {
+      const int i = 16 * t + j;
+      const float xv = (i < count) ? raw[i] : 0.f;
+      if (kStore) {
+        const float xmv = (i > 0 && i - 1 < count) ? raw[i - 1] : 0.f;
+        dbuf[phys_idx(i)] = (T)xv - T(0.97) * (T)xmv;
+      }
+      s += (double)xv;
+    }
+    return s;
+  }
+
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     float* raw = reinterpret_cast<float*>(smem + S::kRawOff + (size_t)it.buf * S::kRawBytes);
-    double* sum16 = reinterpret_cast<double*>(smem + S::kSumOff);    // [kG16] sums of 16 samples
-    double* psum = reinterpret_cast<double*>(smem + S::kPsumOff);    // [5][TF] sums of 80 samples (5 per frame)
+    double* psum80 = reinterpret_cast<double*>(smem + S::kSumOff);   // [kG80] sums of 80 samples
     T* dbuf = reinterpret_cast<T*>(smem + S::kDOff);
     float* sP = reinterpret_cast<float*>(smem + S::kDOff);
     float* sOut = reinterpret_cast<float*>(smem + S::kDOff + S::kPBytes);
@@ -200,71 +259,47 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
       case 0: {   // cooperative staging (the CUDA driver replaces it by a TMA bulk copy when it can)
         for (int i = tid; i < it.count; i += kThreads) raw[i] = it.src[i];
       } break;
-      case 1: {   // pre-emphasis in T into the padded layout + 16-sample partial sums
-        // element i = tid + kThreads j sits at i + (i >> 5) = tid + (tid >> 5) + (kThreads + kThreads / 32) j
-        constexpr int kRowStep = kThreads + kThreads / 32;
-        constexpr int kFull = kSamples / kThreads, kRest = kSamples % kThreads;
-        if (it.count == kSamples) {          // full tile: no bounds checks
-          T* dp = dbuf + tid + (tid >> 5);
-          const float* rp = raw + tid;
-#pragma unroll
-          for (int j = 0; j < kFull; ++j) {
-            const T x = (T)rp[kThreads * j];
-            const T xm = (j == 0 && tid == 0) ? T(0) : (T)rp[kThreads * j - 1];
-            dp[kRowStep * j] = x - T(0.97) * xm;
-          }
-          if (kRest > 0 && tid < kRest)
-            dp[kRowStep * kFull] = (T)rp[kThreads * kFull] - T(0.97) * (T)rp[kThreads * kFull - 1];
-        } else {
-          for (int i = tid; i < kSamples; i += kThreads) {
-            const T x = (i < it.count) ? (T)raw[i] : T(0);
-            const T xm = (i > 0 && i - 1 < it.count) ? (T)raw[i - 1] : T(0);
-            dbuf[phys_idx(i)] = x - T(0.97) * xm;
-          }
+      case 1: {   // pre-emphasis in T into the padded layout + the sums of 80 samples the frame means need
+        // lane l < 30 of warp w owns group t = 30 w + l of 16 samples; five neighbouring lanes make one sum of 80
+        const int l = tid & 31, t = 30 * (tid >> 5) + l;
+        const bool active = l < 30 && t < kG16;
+        const double s16 = active ? group16<true>(raw, dbuf, t, it.count) : 0.0;
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+        const double a = s16 + __shfl_down_sync(0xffffffffu, s16, 1);      // lanes 5 g, 5 g + 2: pairs
+        const double b = a + __shfl_down_sync(0xffffffffu, a, 2);          // lane 5 g: (g0 + g1) + (g2 + g3)
+        const double c5 = b + __shfl_down_sync(0xffffffffu, s16, 4);       //           ... + g4
+        if (active && l % 5 == 0) psum80[t / 5] = c5;
+#else
+        if (active && l % 5 == 0) {   // host emulation runs the lanes one after the other: same tree, recomputed
+          double g[5] = {s16, 0.0, 0.0, 0.0, 0.0};
+          for (int m = 1; m < 5; ++m) g[m] = group16<false>(raw, dbuf, t + m, it.count);
+          psum80[t / 5] = ((g[0] + g[1]) + (g[2] + g[3])) + g[4];
         }
-        if (tid < kG16) {
-          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-          const float* g = raw + tid * 16;
-          if (tid * 16 + 16 <= it.count) {
-            // four 128-bit loads; the starting quad rotates with tid/2 so the 8 lanes of a
-            // quarter-warp hit 8 different 16-byte bank groups (no conflicts)
-            const float4* g4 = reinterpret_cast<const float4*>(g);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const float4 v = g4[(q + (tid >> 1)) & 3];
-              s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
-            }
-          } else {
-            for (int j = 0; j < 16; ++j) s0 += (tid * 16 + j < it.count) ? (double)g[j] : 0.0;
-          }
-          sum16[tid] = (s0 + s1) + (s2 + s3);
-        }
+#endif
       } break;
-      case 2: {   // second level of the frame sums: thread (q, f) adds groups 10 f + 5 q .. + 4
-        if (tid < 5 * TF) {
-          const double* g = sum16 + 10 * f + 5 * role;
-          psum[role * TF + f] = ((g[0] + g[1]) + (g[2] + g[3])) + g[4];
-        }
-      } break;
-      case 3: {   // DC removal + window + stage 1 of the real FFT
-        const double tot = ((psum[f] + psum[TF + f]) + (psum[2 * TF + f] + psum[3 * TF + f])) + psum[4 * TF + f];
+      case 2: {   // DC removal + window + stage 1 of the real FFT
+        const double* p5 = psum80 + 2 * f;      // frame f = samples [160 f, 160 f + 400) = five sums of 80
+        const double tot = ((p5[0] + p5[1]) + (p5[2] + p5[3])) + p5[4];
         const T c = (T)((1.0 - 0.97) * (tot * (1.0 / (double)kFrame)));      // (1 - 0.97) * mean(frame)
         T r[25];
         const T* col = dbuf + (kHop + kHop / 32) * f + role;      // phys_idx(160 f + 16 n1 + role) = 165 f + role + 16 n1 + (n1 >> 1)
-        windowed_column<T>(window + role * kWinRow, r, [col, c](int n1) { return col[16 * n1 + (n1 >> 1)] - c; });
-        rfft512_stage1<T, TF>(r, role, f, tw512, ex);
+        const T* wrow = reinterpret_cast<const T*>(smem + S::kWinOff) + role * kWinRow;
+        const T* twrow = reinterpret_cast<const T*>(smem + S::kTwOff) + role * 32;
+        windowed_column_fn<T>([wrow](int n1) { return wrow[n1]; }, r,
+                              [col, c](int n1) { return col[16 * n1 + (n1 >> 1)] - c; });
+        rfft512_stage1_tw<T, TF>(r, role, f, [twrow](int k1, T& cc, T& ss) { cc = twrow[2 * k1]; ss = twrow[2 * k1 + 1]; }, ex);
       } break;
-      case 4:
+      case 3:
         rfft512_stage2<T, false, TF>(role, f, ex, sP);
         break;
-      case 5: {   // triangular mel bank (generated straight-line code) + floor + log
+      case 4: {   // triangular mel bank (generated straight-line code) + floor + log
         float* row = sOut + f * kOutStride;
         const float lf = log_floor;
         mel_filters_kaldi<TF>(role, f, sP, [row, lf](int m, float acc) {
           row[m] = (acc <= kMelFloor) ? lf : fast_log(acc);
         });
       } break;
-      case 6: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
+      case 5: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
         if (tid < kMel) {
           double s[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, q[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
           if (it.nvalid == TF) {
@@ -305,7 +340,7 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
           }
         }
       } break;
-      case 7: {   // tail: normalise the whole utterance in place (its raw rows are this block's own, L2-hot)
+      case 6: {   // tail: normalise the whole utterance in place (its raw rows are this block's own, L2-hot)
         const float* stat = reinterpret_cast<const float*>(smem + S::kStatOff);
         fbank_normalise_plane(out, mask, it.out_row, it.tp, it.nfr, stat, padding_value, tid, kThreads, 0,
                               (int64_t)it.tp * (kMel / 4));

@@ -19,6 +19,7 @@
 #include <cstdint>
 #include <cmath>
 #include <cstring>
+#include <utility>
 #include <cstdio>
 #include <cstdlib>
 
@@ -125,6 +126,28 @@ AFE_HD void ldg2(const float* p, float& a, float& b) {
   a = v.x; b = v.y;
 }
 
+// a value every lane of the warp holds (e.g. the warp's role): broadcasting it from lane 0 tells the
+// compiler so, and loads indexed by it from the kernel parameters become uniform constant loads
+AFE_HD int warp_uniform(int v) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  return __shfl_sync(0xffffffffu, v, 0);
+#else
+  return v;
+#endif
+}
+
+// optional per-block prologue  void block_init(unsigned char* smem, int tid) const  (tables -> shared memory)
+template <class K, class = void> struct has_block_init { static constexpr bool value = false; };
+template <class K>
+struct has_block_init<K, decltype(std::declval<const K&>().block_init((unsigned char*)nullptr, 0))> {
+  static constexpr bool value = true;
+};
+
+// the thread that derives the next item and issues its TMA copy while the block works on the current
+// one: K::kPrefetchThread if the kernel names a thread whose warp idles in phase 1, else thread 0
+template <class K, class = void> struct prefetch_thread { static constexpr int value = 0; };
+template <class K> struct prefetch_thread<K, decltype((void)K::kPrefetchThread)> { static constexpr int value = K::kPrefetchThread; };
+
 // kernels without per-item context
 struct PlainItem { long item; int buf; int bulk; };
 #define AFE_PLAIN_ITEM                                   \
@@ -192,11 +215,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // it through shared memory and issues its TMA copy while everybody computes item i; the wait
 // on the copy's mbarrier is the only synchronisation before phase 1.  Items whose staging is
 // not a plain copy (edges, unaligned pointers) run phase 0 cooperatively.
-template <class K>
-__global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(const K k) {
+// kTrace (debug, AFE_PHASE_TRACE=1): thread 0 adds the cycles between consecutive barriers to
+// trace[block * 16 + phase] (slot 0 = wait for the staged tile, slot 15 = items processed)
+template <class K, bool kTrace = false>
+__global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(const K k, unsigned long long* trace = nullptr) {
   extern __shared__ __align__(16) unsigned char afe_smem[];
   const long n = k.num_items();
   const int tid = (int)threadIdx.x;
+  if constexpr (has_block_init<K>::value) { k.block_init(afe_smem, tid); __syncthreads(); }
   if constexpr (K::kAsyncStage) {
     __shared__ __align__(8) uint64_t bars[2];
     __shared__ typename K::Item items[2];
@@ -217,28 +243,35 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
       }
     }
     __syncthreads();
-    uint32_t par[2] = {0u, 0u};
+    uint32_t parbits = 0u;                 // bit b = phase parity of staging buffer b's mbarrier
+    long long tacc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // kTrace: cycles per phase (registers)
     for (int it = 0; item < end; ++item, ++it) {
       const int buf = it & 1;
+      long long t0 = 0, tp = 0;
+      if constexpr (kTrace) tp = clock64();
       const typename K::Item cur = items[buf];
-      if (tid == 0 && item + 1 < end) {
+      if (tid == prefetch_thread<K>::value && item + 1 < end) {
         typename K::Item nx = k.next(cur, item + 1);
         nx.buf = buf ^ 1;
         const float* src; int nf;
         nx.bulk = k.stage_src(nx, src, nf) ? 1 : 0;
         items[buf ^ 1] = nx;
         if (nx.bulk) {
-          fence_proxy_async();            // earlier generic-proxy reads of that buffer are done (barriers)
+          // no proxy fence: the buffer's last generic-proxy accesses (phase 1 reads, or the phase 0 copy of an
+          // unaligned tile) were performed before the barriers this thread has since passed
           mbar_expect_tx(&bars[buf ^ 1], (uint32_t)nf * 4u);
           bulk_g2s(afe_smem + K::kStageOff + (size_t)(buf ^ 1) * K::kStageBytes, src, (uint32_t)nf * 4u, &bars[buf ^ 1]);
         }
       }
-      if (cur.bulk) { mbar_wait(&bars[buf], par[buf]); par[buf] ^= 1u; }
+      if (cur.bulk) { mbar_wait(&bars[buf], (parbits >> buf) & 1u); parbits ^= 1u << buf; }
       else { k.phase(0, cur, afe_smem, tid); __syncthreads(); }
+      if constexpr (kTrace) { t0 = clock64(); tacc[0] += t0 - tp; tacc[15] += 1; }
 #pragma unroll
       for (int ph = 1; ph < K::kPhases; ++ph) {
         k.phase(ph, cur, afe_smem, tid);
+        if constexpr (kTrace) { tacc[ph] += clock64() - t0; }            // this warp's own work in the phase
         __syncthreads();
+        if constexpr (kTrace) { const long long t1 = clock64(); tacc[8 + (ph < 7 ? ph : 7)] += t1 - t0; t0 = t1; }   // work + barrier wait
       }
       if constexpr (K::kTailPhases > 0) {     // block-uniform extra phases (e.g. the last tile of a waveform)
         if (k.tail(cur)) {
@@ -246,9 +279,13 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
           for (int ph = K::kPhases; ph < K::kPhases + K::kTailPhases; ++ph) {
             k.phase(ph, cur, afe_smem, tid);
             __syncthreads();
+            if constexpr (kTrace) { const long long t1 = clock64(); tacc[7] += t1 - t0; t0 = t1; }
           }
         }
       }
+    }
+    if constexpr (kTrace) {     // lane 0 of every warp: trace[(block * 32 + warp) * 16 + slot]
+      if ((tid & 31) == 0) for (int i = 0; i < 16; ++i) trace[((size_t)blockIdx.x * 32 + (tid >> 5)) * 16 + i] = (unsigned long long)tacc[i];
     }
   } else {
     for (long item = blockIdx.x; item < n; item += gridDim.x) {
@@ -283,6 +320,44 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t strea
     }
   }
   long grid = n < (long)max_blocks ? n : (long)max_blocks;
+  if constexpr (K::kAsyncStage) {
+    static const bool tracing = std::getenv("AFE_PHASE_TRACE") != nullptr;
+    if (tracing) {      // debug only: synchronous, prints the mean cycles per item each phase took (per block, thread 0)
+      const void* tfn = (const void*)phased_kernel<K, true>;
+      cudaFuncSetAttribute(tfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      cudaFuncSetAttribute(tfn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+      unsigned long long* tr = nullptr;
+      const size_t nslots = (size_t)grid * 32 * 16;
+      cudaMallocManaged(&tr, sizeof(unsigned long long) * nslots);
+      std::memset(tr, 0, sizeof(unsigned long long) * nslots);
+      phased_kernel<K, true><<<(unsigned)grid, K::kThreads, smem_bytes, stream>>>(k, tr);
+      cudaStreamSynchronize(stream);
+      // per phase: this-warp work (min / mean / max over the block's warps) and wall = work + barrier wait (warp 0)
+      const int nw = K::kThreads / 32;
+      double wmin[8] = {0}, wmean[8] = {0}, wmax[8] = {0}, wall[8] = {0}, items = 0;
+      for (long b = 0; b < grid; ++b) {
+        const double it_b = (double)tr[(size_t)b * 32 * 16 + 15];
+        items += it_b;
+        for (int p = 0; p < 8; ++p) {
+          double mn = 1e30, mx = 0, sm = 0;
+          for (int w = 0; w < nw; ++w) { const double v = (double)tr[((size_t)b * 32 + w) * 16 + p]; mn = v < mn ? v : mn; mx = v > mx ? v : mx; sm += v; }
+          wmin[p] += mn; wmax[p] += mx; wmean[p] += sm / nw;
+          wall[p] += (double)tr[((size_t)b * 32) * 16 + 8 + p];
+        }
+      }
+      std::fprintf(stderr, "[afe trace] %s: %ld blocks, %.0f items; cycles per item, phase: warp work min/mean/max -> wall\n", __PRETTY_FUNCTION__, grid, items);
+      double tot = wmean[0] / items;
+      std::fprintf(stderr, "[afe trace]   prologue+wait %.0f/%.0f/%.0f\n", wmin[0] / items, wmean[0] / items, wmax[0] / items);
+      for (int p = 1; p < 8; ++p) {
+        if (wall[p] == 0) continue;
+        std::fprintf(stderr, "[afe trace]   phase %d%s: %.0f/%.0f/%.0f -> %.0f\n", p, p == 7 ? " (tail)" : "", wmin[p] / items, wmean[p] / items, wmax[p] / items, wall[p] / items);
+        tot += wall[p] / items;
+      }
+      std::fprintf(stderr, "[afe trace]   total %.0f\n", tot);
+      cudaFree(tr);
+      return 0;
+    }
+  }
   phased_kernel<K><<<(unsigned)grid, K::kThreads, smem_bytes, stream>>>(k);
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { note_error("kernel launch", cudaGetErrorString(e)); return -1; }
@@ -311,6 +386,8 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
     for (long block = 0; block < grid; ++block) {
       const long first = block * per, end = first + per < n ? first + per : n;
       typename K::Item ic{};
+      if constexpr (has_block_init<K>::value)
+        for (int tid = 0; tid < K::kThreads; ++tid) k.block_init(smem, tid);
       for (long item = first; item < end; ++item) {
         ic = (item == first) ? k.prepare(item) : k.next(ic, item);
         ic.buf = (int)((item - first) & 1);              // exercise both staging buffers

@@ -41,7 +41,7 @@ constexpr int kTileFrames = 32;
 constexpr int kRoles = 16;
 constexpr int kWinRow = 26;          // window tables are role-major: w[role][n1] = window[16 n1 + role], 25 used
 
-// the 25 windowed samples of (role, frame): table entries fetched two per load
+// the 25 windowed samples of (role, frame): global table entries fetched two per load
 template <typename T, class Sample>
 AFE_HD void windowed_column(const T* AFE_RESTRICT wrow, T (&r)[25], Sample sample) {
 #pragma unroll
@@ -52,10 +52,21 @@ AFE_HD void windowed_column(const T* AFE_RESTRICT wrow, T (&r)[25], Sample sampl
   }
   r[24] = ldg(wrow + 24) * sample(24);
 }
+// same with the window row read through win(n1) (a table that rides in the kernel parameters)
+template <typename T, class Win, class Sample>
+AFE_HD void windowed_column_fn(Win win, T (&r)[25], Sample sample) {
+#pragma unroll
+  for (int n1 = 0; n1 < 25; ++n1) r[n1] = win(n1) * sample(n1);
+}
 
-template <typename T, int TF = kTileFrames>
-AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRICT tw512,
-                           cplx<T>* AFE_RESTRICT ex) {
+// twiddle accessors for rfft512_stage1: tw(k1, c, s) yields W512^(n2 k1) = c + i s of the caller's n2
+template <typename T> struct TwGlobal {           // [16][16][2] table in global memory
+  const T* AFE_RESTRICT row;                       // tw512 + n2 * 32
+  AFE_HD void operator()(int k1, T& c, T& s) const { ldg2(row + k1 * 2, c, s); }
+};
+
+template <typename T, int TF = kTileFrames, class Tw>
+AFE_HD void rfft512_stage1_tw(const T (&r)[25], int n2, int f, Tw tw, cplx<T>* AFE_RESTRICT ex) {
   T re[16], im[16];
 #pragma unroll
   for (int m = 0; m < 12; ++m) { re[m] = r[2 * m]; im[m] = r[2 * m + 1]; }
@@ -82,9 +93,15 @@ AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRIC
 #pragma unroll
   for (int k1 = 1; k1 < 16; ++k1) {
     T c, s;                                                                                   // c + i s
-    ldg2(tw512 + (n2 * 16 + k1) * 2, c, s);
+    tw(k1, c, s);
     ex[(k1 * 16 + n2) * TF + f] = cplx<T>{re[k1] * c - im[k1] * s, re[k1] * s + im[k1] * c};
   }
+}
+
+template <typename T, int TF = kTileFrames>
+AFE_HD void rfft512_stage1(const T (&r)[25], int n2, int f, const T* AFE_RESTRICT tw512,
+                           cplx<T>* AFE_RESTRICT ex) {
+  rfft512_stage1_tw<T, TF>(r, n2, f, TwGlobal<T>{tw512 + n2 * 32}, ex);
 }
 
 AFE_HD float rfft_mag(float p) {
