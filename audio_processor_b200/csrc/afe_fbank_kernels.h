@@ -128,10 +128,10 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   static constexpr size_t kStageBytes = S::kRawBytes;
   static constexpr int kSamples = S::kSamples;
   static constexpr int kG16 = S::kG16;
-  static constexpr int kStoreFirst = 96;        // threads [96, kThreads) move the tile's rows to global memory
+  static constexpr int kStoreFirst = 4 * kMel;  // threads [320, kThreads) move the tile's rows to global memory
   static constexpr int kG80 = S::kG80;
   static constexpr int kPrefetchThread = kThreads - 32;   // lane 0 of the last warp: it has no group in phase 1
-  static_assert((kG16 + 29) / 30 * 32 <= kThreads - 32 && kMel <= kStoreFirst, "phase thread budgets");
+  static_assert((kG16 + 29) / 30 * 32 <= kThreads - 32 && kStoreFirst < kThreads, "phase thread budgets");
 
   struct Item { long item; int buf; int bulk; int b; int f0; int nfr; int nvalid; int count; int whole; int tp;
                 const float* src; int64_t out_row; };
@@ -196,6 +196,26 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   AFE_HD bool stage_src(const Item& it, const float*& src, int& nfloats) const {
     src = it.src; nfloats = it.count;
     return (reinterpret_cast<uintptr_t>(it.src) & 15u) == 0;
+  }
+
+  // (sum, sum of squares) in float64 of mel bin m over quarter q4 of the tile's valid frames
+  AFE_HD static void quarter_sums(const float* sOut, int m, int q4, int nvalid, double& s, double& ss) {
+    constexpr int kQ = TF / 4;
+    double s0 = 0.0, s1 = 0.0, q0 = 0.0, q1 = 0.0;
+    const float* col = sOut + (q4 * kQ) * kOutStride + m;
+    if ((q4 + 1) * kQ <= nvalid) {
+#pragma unroll
+      for (int i = 0; i < kQ; i += 2) {
+        const double a = (double)col[i * kOutStride], b = (double)col[(i + 1) * kOutStride];
+        s0 += a; q0 += a * a; s1 += b; q1 += b * b;
+      }
+    } else {
+      for (int i = 0; i < kQ && q4 * kQ + i < nvalid; ++i) {
+        const double a = (double)col[i * kOutStride];
+        s0 += a; q0 += a * a;
+      }
+    }
+    s = s0 + s1; ss = q0 + q1;
   }
 
   // Samples [16 t, 16 t + 16) of the tile: pre-emphasis x[n] - 0.97 x[n-1] in T into the padded layout
@@ -300,34 +320,36 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
         });
       } break;
       case 5: {   // per-bin partial statistics (float64) + coalesced store of the raw log-mel
-        if (tid < kMel) {
-          double s[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, q[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-          if (it.nvalid == TF) {
-#pragma unroll
-            for (int j = 0; j < TF; ++j) {
-              const double v = (double)sOut[j * kOutStride + tid];
-              s[j & 7] += v; q[j & 7] += v * v;
-            }
-          } else {
-            for (int j = 0; j < it.nvalid; ++j) {
-              const double v = (double)sOut[j * kOutStride + tid];
-              s[0] += v; q[0] += v * v;
-            }
+        if (tid < 4 * kMel) {
+          // four lanes per mel bin, TF / 4 frames each, combined as (p0 + p1) + (p2 + p3)
+          const int m = tid >> 2, q4 = tid & 3;
+          double ts, tq;
+          quarter_sums(sOut, m, q4, it.nvalid, ts, tq);
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+          ts += __shfl_xor_sync(0xffffffffu, ts, 1); tq += __shfl_xor_sync(0xffffffffu, tq, 1);
+          ts += __shfl_xor_sync(0xffffffffu, ts, 2); tq += __shfl_xor_sync(0xffffffffu, tq, 2);
+#else
+          if (q4 == 0) {     // host emulation: the same tree, the other three quarters recomputed here
+            double s1, q1, s2, q2, s3, q3;
+            quarter_sums(sOut, m, 1, it.nvalid, s1, q1);
+            quarter_sums(sOut, m, 2, it.nvalid, s2, q2);
+            quarter_sums(sOut, m, 3, it.nvalid, s3, q3);
+            ts = (ts + s1) + (s2 + s3); tq = (tq + q1) + (q2 + q3);
           }
-          const double ts = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
-          const double tq = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+#endif
+          if (q4 != 0) break;
           if (!it.whole) {
-            partials[(it.item * kMel + tid) * 2] = ts;
-            partials[(it.item * kMel + tid) * 2 + 1] = tq;
+            partials[(it.item * kMel + m) * 2] = ts;
+            partials[(it.item * kMel + m) * 2 + 1] = tq;
           } else {
             // same in-order float64 reduction over the tiles as FbankStatsKernel, kept in shared memory
             double* acc = reinterpret_cast<double*>(smem + S::kAccOff);
-            const double as = (it.f0 == 0) ? 0.0 + ts : acc[2 * tid] + ts;
-            const double aq = (it.f0 == 0) ? 0.0 + tq : acc[2 * tid + 1] + tq;
-            acc[2 * tid] = as; acc[2 * tid + 1] = aq;
+            const double as = (it.f0 == 0) ? 0.0 + ts : acc[2 * m] + ts;
+            const double aq = (it.f0 == 0) ? 0.0 + tq : acc[2 * m + 1] + tq;
+            acc[2 * m] = as; acc[2 * m + 1] = aq;
             if (it.f0 + TF >= it.nfr) {
               float* stat = reinterpret_cast<float*>(smem + S::kStatOff);
-              fbank_mean_den(as, aq, it.nfr, stat[2 * tid], stat[2 * tid + 1]);
+              fbank_mean_den(as, aq, it.nfr, stat[2 * m], stat[2 * m + 1]);
             }
           }
         } else if (tid >= kStoreFirst) {
