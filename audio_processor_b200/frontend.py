@@ -31,6 +31,20 @@ class FrontendResult:
     waveforms: List[Tuple[torch.Tensor, torch.Tensor]] = field(default_factory=list)   # (stereo16k (2,L'), mixed (1,L'))
 
 
+@dataclass
+class _Plan:
+    """Everything about a batch of calls that depends on their lengths only."""
+    call_seconds: float
+    chunks: List[Tuple[int, int, int, int]]
+    lens: List[int]
+    first_chunk: List[int]
+    order: List[int]
+    tps: List[int]
+    total_rows: int
+    row_of: List[int]
+    tp_of: List[int]
+
+
 class CallFrontend:
     def __init__(self, device=None, chunk_duration_sec=25, overlap_sec=1, target_sample_rate=16000,
                  batch_size=16, padding_value=0.0, precision=_native.PRECISION_F64, acoustic=True):
@@ -44,6 +58,7 @@ class CallFrontend:
         self.precision = precision
         self.acoustic = acoustic
         self._tables = {}
+        self._plans: Dict[tuple, _Plan] = {}
         self._copy_stream = None
 
     def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True,
@@ -56,44 +71,15 @@ class CallFrontend:
         Every integer of the result (chunk table, length-sorted order, the padded length of
         each batch of ``batch_size`` chunks, the output row of every chunk) depends on the call
         lengths only, so the whole output layout is planned on the host first.  The calls are
-        then processed in sub-batches of ``sub_batch`` calls: while sub-batch k is resampled,
+        then processed in sub-batches (``sub_batch`` calls each, or adaptively -- ``_next_group``):
+        every upload is enqueued on a second stream at once; while sub-batch k is resampled,
         featurised (all three streams in one launch, each chunk written to its final rows)
-        and its acoustic rows computed, sub-batch k+1 is uploaded on a second stream."""
+        and its acoustic rows computed, the later calls keep crossing PCIe."""
         fe, sr_t, dev = self.fe, self.target_sample_rate, self.device
         res = FrontendResult(n_calls=len(calls))
-        chunk_samples = int(self.chunk_duration_sec * sr_t)
-        step = chunk_samples - int(self.overlap_sec * sr_t)
-        # ---- plan (host, integers only)
-        louts, first_chunk, lens = [], [], []
-        for ci, call in enumerate(calls):
-            L = int(call.shape[1])
-            res.call_seconds += L / float(sample_rate)
-            Lr = fe.resampled_length(L, sample_rate, sr_t) if sample_rate != sr_t else L
-            louts.append(Lr)
-            first_chunk.append(len(res.chunks))
-            for idx, (s, e) in enumerate(self._chunk_table(Lr, chunk_samples, step)):
-                res.chunks.append((ci, idx, s, e)); lens.append(e - s)
-        first_chunk.append(len(res.chunks))
-        n = len(res.chunks)
-        if n == 0:
-            return res
-        G = self.batch_size
-        res.order = sorted(range(n), key=lens.__getitem__)       # transcribe_batch: stable sort by length
-        slens = [lens[i] for i in res.order]
-        tps, total_rows = fe.fbank_layout(slens, G)
-        row_of, tp_of, pos = [0] * n, [0] * n, 0
-        for g, tp in enumerate(tps):
-            for j in range(g * G, min(n, (g + 1) * G)):
-                row_of[res.order[j]] = pos; tp_of[res.order[j]] = tp; pos += tp
-        half = total_rows // 2
-        feat_all = torch.empty((3 * half, 160), dtype=torch.float32, device=dev)
-        mask_all = torch.empty((3 * half,), dtype=torch.int32, device=dev)
-        if self.acoustic:
-            rows = torch.empty((2 * n, 38), dtype=torch.float32, device=dev)
-            status = torch.empty((2 * n,), dtype=torch.int32, device=dev)
-        # ---- pipeline over sub-batches of calls
+        # ---- uploads first: the copy of sub-batch 0 crosses PCIe while the host plans the layout
         any_host = any(not c.is_cuda for c in calls)
-        sb = int(sub_batch) if sub_batch else (8 if any_host else len(calls))
+        groups = self._schedule(len(calls), sub_batch, any_host)       # [(first call, end call)] per sub-batch
         main = torch.cuda.current_stream(dev)
         if any_host and self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(dev)
@@ -115,31 +101,47 @@ class CallFrontend:
                     xdev[i] = xin[offs[i]:offs[i] + c.numel() * c.element_size()].view(c.dtype).view(c.shape)
             self._copy_stream.wait_stream(main)
 
-        def upload(k0):
-            sub = range(k0, min(k0 + sb, len(calls)))
-            if not any_host:
-                return [calls[i].to(dev) for i in sub], None
-            xs = []
+        # every host call is enqueued on the copy stream right away, one event per call; device calls
+        # (and host calls of an unsupported layout) take the ordinary .to(dev) path
+        xs_all: List[torch.Tensor] = [None] * len(calls)           # type: ignore[list-item]
+        evs: List[Optional[torch.cuda.Event]] = [None] * len(calls)
+        if any_host:
             with torch.cuda.stream(self._copy_stream):
-                for i in sub:
+                for i, c in enumerate(calls):
                     if xdev[i] is None:
-                        xs.append(calls[i].to(dev))
+                        xs_all[i] = c.to(dev)
                     else:
-                        xdev[i].copy_(calls[i], non_blocking=True)
-                        xs.append(xdev[i])
-                ev = torch.cuda.Event()
-                ev.record(self._copy_stream)
-            return xs, ev
-
-        starts = list(range(0, len(calls), sb))
-        pending = upload(starts[0])
+                        xdev[i].copy_(c, non_blocking=True)
+                        xs_all[i] = xdev[i]
+                        evs[i] = torch.cuda.Event()
+                        evs[i].record(self._copy_stream)
+        else:
+            xs_all = [c.to(dev) for c in calls]
+        # ---- plan (host, integers only; cached by the call lengths it depends on)
+        plan = self._plan(tuple(int(c.shape[1]) for c in calls), int(sample_rate))
+        res.call_seconds = plan.call_seconds
+        res.chunks, res.order = plan.chunks, plan.order
+        lens, first_chunk, tps, total_rows = plan.lens, plan.first_chunk, plan.tps, plan.total_rows
+        row_of, tp_of = plan.row_of, plan.tp_of
+        n = len(res.chunks)
+        if n == 0:
+            return res
+        G = self.batch_size
+        half = total_rows // 2
+        feat_all = torch.empty((3 * half, 160), dtype=torch.float32, device=dev)
+        mask_all = torch.empty((3 * half,), dtype=torch.int32, device=dev)
+        if self.acoustic:
+            rows = torch.empty((2 * n, 38), dtype=torch.float32, device=dev)
+            status = torch.empty((2 * n,), dtype=torch.int32, device=dev)
         res.waveforms = [None] * len(calls)                       # type: ignore[list-item]
-        for si, k0 in enumerate(starts):
-            xs, ev = pending
-            if si + 1 < len(starts):
-                pending = upload(starts[si + 1])                  # enqueue the next upload before this compute
-            if ev is not None:
-                main.wait_event(ev)
+        done_prev: Optional[torch.cuda.Event] = None
+        k0 = 0
+        while k0 < len(calls):
+            k1 = self._next_group(k0, len(calls), evs, groups)
+            xs = xs_all[k0:k1]
+            last_ev = next((evs[i] for i in range(k1 - 1, k0 - 1, -1) if evs[i] is not None), None)
+            if last_ev is not None:
+                main.wait_event(last_ev)                          # copies complete in order on the copy stream
             # resample / mix: stereo and mono calls of the sub-batch, one launch each
             for want_rows in (2, 1):
                 ids = [k0 + j for j, x in enumerate(xs) if int(x.shape[0]) == want_rows]
@@ -159,8 +161,9 @@ class CallFrontend:
             bad = [k0 + j for j, x in enumerate(xs) if int(x.shape[0]) not in (1, 2)]
             if bad:
                 raise ValueError(f"process_calls: call {bad[0]} has {int(xs[bad[0] - k0].shape[0])} channels")
-            c0, c1 = first_chunk[k0], first_chunk[min(k0 + sb, len(calls))]
+            c0, c1 = first_chunk[k0], first_chunk[k1]
             if c1 == c0:
+                k0 = k1
                 continue
             mixed_p, agent_p, client_p = [], [], []
             for ci, _, s, _ in res.chunks[c0:c1]:
@@ -178,6 +181,14 @@ class CallFrontend:
             if self.acoustic:
                 fe.acoustic_ptrs(agent_p + client_p, sub_lens * 2, sr_t, out=rows, status=status,
                                  out_index=list(range(c0, c1)) + list(range(n + c0, n + c1)))
+            if groups is None and k1 < len(calls):
+                # adaptive grouping: at most two groups in flight, so the next group is formed from
+                # what has ARRIVED by the time the GPU is about to need it
+                done = torch.cuda.Event(); done.record(main)
+                if done_prev is not None:
+                    done_prev.synchronize()
+                done_prev = done
+            k0 = k1
         for si, key in enumerate(("stereo", "agent", "client")):
             views, r = [], si * half
             for g, tp in enumerate(tps):
@@ -190,6 +201,68 @@ class CallFrontend:
                 rows = rows.cpu(); status = status.cpu()
             res.acoustic_rows, res.acoustic_status = rows, status
         return res
+
+    @staticmethod
+    def _schedule(n_calls: int, sub_batch: Optional[int], any_host: bool) -> Optional[List[Tuple[int, int]]]:
+        """Fixed sub-batches of calls, or None for the adaptive grouping of host calls (_next_group)."""
+        if n_calls <= 0:
+            return []
+        if sub_batch:
+            sb = int(sub_batch)
+            return [(k, min(k + sb, n_calls)) for k in range(0, n_calls, sb)]
+        if not any_host:
+            return [(0, n_calls)]
+        return None
+
+    kFirstGroup, kMinGroup, kMaxGroup = 2, 4, 16
+
+    def _next_group(self, k0: int, n_calls: int, evs, groups) -> int:
+        """End of the sub-batch that starts at call k0.  Adaptive mode: wait for ``kMinGroup`` calls to
+        have crossed PCIe, then take every further call that has already arrived, up to ``kMaxGroup``.
+        When PCIe is the bound the groups stay small (the step ends ``upload(all) + compute(last
+        group)``); when the kernels are, uploads run ahead and the groups grow to launches that fill
+        the GPU and normalise most utterances inside the fbank kernel."""
+        if groups is not None:
+            return next(k1 for (g0, k1) in groups if g0 == k0)
+        k1 = min(k0 + (self.kMinGroup if k0 > 0 else self.kFirstGroup), n_calls)   # nothing to overlap the first upload with
+        ev = next((evs[i] for i in range(k1 - 1, k0 - 1, -1) if evs[i] is not None), None)
+        if ev is not None:
+            ev.synchronize()
+        while k1 < n_calls and k1 - k0 < self.kMaxGroup and (evs[k1] is None or evs[k1].query()):
+            k1 += 1
+        return k1
+
+    def _plan(self, lengths: Tuple[int, ...], sample_rate: int) -> _Plan:
+        """Chunk table of every call (split_audio, audio_processor.py:115-160), the stable length sort of
+        transcribe_batch (:170-181), the padded length of each batch of ``batch_size`` chunks and the
+        output row of every chunk.  Cached: batches of equally long calls repeat."""
+        key = (lengths, sample_rate)
+        plan = self._plans.get(key)
+        if plan is not None:
+            return plan
+        fe, sr_t = self.fe, self.target_sample_rate
+        chunk_samples = int(self.chunk_duration_sec * sr_t)
+        step = chunk_samples - int(self.overlap_sec * sr_t)
+        chunks, lens, first_chunk, seconds = [], [], [], 0.0
+        for ci, L in enumerate(lengths):
+            seconds += L / float(sample_rate)
+            Lr = fe.resampled_length(L, sample_rate, sr_t) if sample_rate != sr_t else L
+            first_chunk.append(len(chunks))
+            for idx, (s, e) in enumerate(self._chunk_table(Lr, chunk_samples, step)):
+                chunks.append((ci, idx, s, e)); lens.append(e - s)
+        first_chunk.append(len(chunks))
+        n, G = len(chunks), self.batch_size
+        order = sorted(range(n), key=lens.__getitem__)           # transcribe_batch: stable sort by length
+        tps, total_rows = fe.fbank_layout([lens[i] for i in order], G) if n else ([], 0)
+        row_of, tp_of, pos = [0] * n, [0] * n, 0
+        for g, tp in enumerate(tps):
+            for j in range(g * G, min(n, (g + 1) * G)):
+                row_of[order[j]] = pos; tp_of[order[j]] = tp; pos += tp
+        plan = _Plan(seconds, chunks, lens, first_chunk, order, list(tps), int(total_rows), row_of, tp_of)
+        if len(self._plans) >= 64:
+            self._plans.pop(next(iter(self._plans)))
+        self._plans[key] = plan
+        return plan
 
     def _chunk_table(self, total: int, chunk: int, step: int):
         key = (total, chunk, step)
