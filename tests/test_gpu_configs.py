@@ -1,0 +1,161 @@
+"""BASELINE.json configs cfg2 / cfg3 / cfg5 on the CUDA path: oracle parity at sizes the oracle finishes
+in seconds, and size-independent properties at the full sizes.  Needs a B200 (``pytest -m gpu``)."""
+import numpy as np
+import pytest
+
+from oracle import np_acoustic, np_fbank, np_resample, np_tables
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fe():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from audio_processor_b200 import runtime
+    return runtime.get_frontend(0)
+
+
+def _cmp_nan(a, b, tol):
+    assert a.shape == b.shape
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = ~np.isnan(b)
+    err = float(np.max(np.abs(a[ok] - b[ok]), initial=0.0))
+    assert err <= tol, err
+
+
+def _acoustic_close(got, ref, rel=1e-4, floor=1e-3):
+    got = np.asarray(got, np.float64); ref = np.asarray(ref, np.float64)
+    assert got[11] == ref[11]                                     # tempo: exact
+    bad = [(k, got[k], ref[k]) for k in range(38) if abs(got[k] - ref[k]) > max(floor, rel * abs(ref[k]))]
+    assert not bad, bad
+
+
+# ------------------------------------------------------------------ cfg3: VAD-style ragged segments
+def test_cfg3_ragged_segments_fbank_and_acoustic(fe):
+    """0.5-30 s segments incl. the forced edge lengths, featurised in length-sorted batches of 16 exactly like
+    SpeechSegment.transcribe_segments_batched (speech_segment.py:199-232), and their 38 acoustic features."""
+    from audio_processor_b200 import SpeechSegment, acoustic, synth
+    segs, sr = synth.cfg3_segments(37)
+    lens = [int(s.shape[1]) for s in segs]
+    assert lens[:5] == list(synth.CFG3_EDGE_LENGTHS)
+    seg = SpeechSegment({"gpu_index": 0, "batch_size": 16})
+    items = [{"segment_waveform": s.to(fe.device), "start": 0.0, "end": n / sr, "speaker": "client"} for s, n in zip(segs, lens)]
+    groups = seg.featurise_segments(items, sr)
+    order = sorted(range(len(lens)), key=lens.__getitem__)
+    assert [i for idxs, _, _ in groups for i in idxs] == order     # stable sort by length, batches of 16
+    assert [len(idxs) for idxs, _, _ in groups] == [16, 16, 5]
+    for idxs, feat, mask in groups:
+        ref_f, ref_m = np_fbank.featurise([segs[i][0].numpy() for i in idxs])
+        assert tuple(feat.shape) == ref_f.shape
+        assert np.array_equal(mask.cpu().numpy(), ref_m)            # bit-exact masks / padded lengths
+        _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+    # acoustic features of the edge lengths and a few random ones
+    pick = [0, 1, 2, 3, 4, 9, 17, 30]
+    feats = acoustic.extract_acoustic_features_batch([segs[i][0].numpy() for i in pick], sr, fe.device)
+    for i, f in zip(pick, feats):
+        ref = np_acoustic.acoustic_features(segs[i][0].numpy())
+        assert list(f.keys()) == list(ref.keys())
+        _acoustic_close(list(f.values()), list(ref.values()))
+
+
+# ------------------------------------------------------------------ cfg5: 44.1 kHz long form
+def test_cfg5_44k_resample_chunks_and_long_fbank(fe):
+    import torch
+    from audio_processor_b200 import AudioProcessor, synth
+    # (a) generic 441 -> 160 polyphase resampler, bit-exact against the oracle on 12 s
+    x, sr = synth.cfg5_longform(12.0)
+    assert sr == 44100
+    y = fe.resample(x.to(fe.device), sr, 16000)
+    ref = np_resample.resample(x.numpy(), sr, 16000)
+    assert y.shape[1] == int(np.ceil(x.shape[1] * 16000 / 44100)) == ref.shape[1]
+    assert np.array_equal(y.cpu().numpy(), ref)
+    # (b) the integer contract at the full 1-hour size (host only): 150 chunks, 149 full + 384000
+    L16 = fe.resampled_length(158_760_000, 44100, 16000)
+    assert L16 == 57_600_000
+    table = np_tables.chunk_table(L16, 16000, 25, 1)
+    ap = AudioProcessor({"chunk_duration_sec": 25, "overlap_sec": 1, "target_sample_rate": 16000, "batch_size": 16, "gpu_index": 0})
+    from audio_processor_b200.audio_processor import chunk_table
+    mine = chunk_table(L16, 400_000, 384_000)
+    assert [(s, e) for s, e, _, _ in table] == [(s, e) for s, e in mine]
+    assert len(mine) == 150 and mine[-1] == (57_216_000, 57_600_000) and all(e - s == 400_000 for s, e in mine[:-1])
+    # (c) one unchunked processor([x]) call on a long waveform: 10 min = 59 998 frames against the oracle,
+    #     and a mono call goes through split_audio with all three streams aliasing one tensor
+    x10, _ = synth.cfg5_longform(600.0 * 16000 / 44100)            # 600 s worth of 16 kHz samples at 44.1 kHz pace
+    y10 = fe.resample(x10.to(fe.device), 44100, 16000)[0]
+    T = 1 + (y10.numel() - 400) // 160
+    feat, mask = fe.fbank([y10])
+    assert tuple(feat.shape) == (1, (T + 1) // 2, 160) and int(mask.sum()) == T // 2
+    ref_f, ref_m = np_fbank.featurise([y10.cpu().numpy()])
+    assert np.array_equal(mask.cpu().numpy(), ref_m)
+    _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+    chunks, agent, client = ap.split_audio(x, 44100, "long.wav")
+    assert agent.data_ptr() == client.data_ptr() and len(chunks) == 1
+    assert torch.equal(chunks[0]["stereo_waveform"], chunks[0]["agent_waveform"])
+
+
+def test_cfg5_long_sequence_properties(fe):
+    """The 1-hour stress shape: 359 998 frames in ONE utterance (per-utterance statistics span 11 250 tiles
+    and every block of the launch).  Properties: frame count, mask, zero mean / unit variance per mel bin."""
+    import torch
+    n = 57_600_000
+    g = torch.Generator(device=fe.device).manual_seed(9)
+    y = torch.rand(n, generator=g, device=fe.device) - 0.5
+    y[1_000_000:1_500_000] = 0.0                                    # a stretch of digital silence
+    feat, mask = fe.fbank([y])
+    T = 1 + (n - 400) // 160
+    assert T == 359_998 and tuple(feat.shape) == (1, T // 2, 160) and int(mask.sum()) == T // 2
+    f = feat.view(-1, 80)[:T].double()
+    assert torch.isfinite(f).all()
+    assert float(f.mean(0).abs().max()) < 1e-4
+    assert float((f.var(0, unbiased=True) - 1.0).abs().max()) < 1e-3
+
+
+# ------------------------------------------------------------------ cfg2 at full size: properties + spot parity
+def test_cfg2_full_size_properties_and_spot_parity(fe):
+    import torch
+    from audio_processor_b200 import CallFrontend, synth
+    calls, sr = synth.cfg2_calls(64, 300.0, distinct=3)
+    cf = CallFrontend(fe.device)
+    res = cf.process_calls([c.pin_memory() for c in calls], sr)
+    n = len(res.chunks)
+    assert n == 64 * 13 and abs(res.call_seconds - 64 * 300.0) < 1e-6
+    # chunk table of every call: 12 x 400000 + 192000, starts 384000 apart (bit-exact integers)
+    per_call = [(s, e) for c, _, s, e in res.chunks if c == 5]
+    assert per_call == [(384000 * i, min(384000 * i + 400000, 4_800_000)) for i in range(13)]
+    # length-sorted batches of 16: 4 batches of the 64 short chunks, then full chunks
+    lens = [e - s for _, _, s, e in res.chunks]
+    assert res.order == sorted(range(n), key=lens.__getitem__)
+    for key in ("stereo", "agent", "client"):
+        views = res.features[key]
+        assert len(views) == 52
+        for g, (feat, mask) in enumerate(views):
+            exp_T = 1 + (max(lens[i] for i in res.order[16 * g:16 * g + 16]) - 400) // 160
+            assert tuple(feat.shape) == (16, (exp_T + 1) // 2, 160)
+            assert mask.sum(1).tolist() == [(1 + (lens[i] - 400) // 160) // 2 for i in res.order[16 * g:16 * g + 16]]
+        assert all(torch.isfinite(f).all() for f, _ in views)
+    # identical calls give identical outputs wherever they land (calls 0, 3, 6, ... are the same waveform)
+    a = res.order.index(0 * 13 + 2); b = res.order.index(3 * 13 + 2)
+    fa = res.features["client"][a // 16][0][a % 16]; fb = res.features["client"][b // 16][0][b % 16]
+    assert torch.equal(fa, fb)
+    assert torch.equal(res.acoustic_rows[0 * 13 + 2], res.acoustic_rows[3 * 13 + 2])
+    assert int(res.acoustic_status.sum()) == 0
+    # spot parity against the oracle: one full chunk and the short tail chunk of call 1, agent stream
+    ref = np_resample.resample(calls[1].numpy(), sr, 16000)
+    assert np.array_equal(res.waveforms[1][0].cpu().numpy(), ref)
+    for chunk_idx in (4, 12):
+        j = 1 * 13 + chunk_idx
+        pos = res.order.index(j)
+        feat, mask = res.features["agent"][pos // 16]
+        s, e = res.chunks[j][2], res.chunks[j][3]
+        T = 1 + (e - s - 400) // 160
+        Tp = feat.shape[1] * 2
+        ref_f, _ = np_fbank.featurise([ref[0, s:e]])
+        got = feat[pos % 16].reshape(Tp, 80)[:T - (T % 2)].cpu().numpy()
+        assert np.max(np.abs(got - ref_f.reshape(-1, 80)[:T - (T % 2)])) <= 1e-3
+        ref_a = np_acoustic.acoustic_features(ref[0, s:e])
+        vals = res.acoustic_rows[j].tolist()
+        from audio_processor_b200.acoustic import TEMPO_SLOT, _tempo
+        vals[TEMPO_SLOT] = _tempo(vals[TEMPO_SLOT], e - s, 16000)
+        _acoustic_close(vals, list(ref_a.values()))
