@@ -58,8 +58,11 @@ struct AcSmem {
   static constexpr size_t kRedOff = kFxOff + sizeof(float) * 512;
   static constexpr size_t kPfOff = kRedOff + sizeof(float) * 512;
   static constexpr size_t kThrOff = kPfOff + sizeof(float) * 8 * 32;
-  static constexpr size_t kBytes = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;
-  static_assert(kThrOff + sizeof(float) * 64 <= kBytes, "ex region too small");
+  static constexpr size_t kDsumOff = kThrOff + sizeof(float) * 64;                   // double dsum[3][32]: total, sum m k, sum m k^2
+  static constexpr size_t kHannOff = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // float hann[16][26] (block_init)
+  static constexpr size_t kTwOff = kHannOff + sizeof(float) * kRoles * kWinRow;               // float tw512[16][16][2]
+  static constexpr size_t kBytes = kTwOff + sizeof(float) * kRoles * 32;
+  static_assert(kDsumOff % 8 == 0 && kDsumOff + sizeof(double) * 96 <= kHannOff, "ex region too small");
 };
 
 // sqrt for magnitudes: one MUFU (max relative error ~1 ulp); the reference's float32 |X| carries
@@ -82,6 +85,7 @@ struct AcousticTileKernel {
   static constexpr bool kAsyncStage = true;
   static constexpr size_t kStageOff = AcSmem::kRawOff;
   static constexpr size_t kStageBytes = AcSmem::kRawBytes;
+  static constexpr int kPrefetchThread = kThreads - 32;   // lane 0 of the last warp: the lightest one in phase 1
 
   struct Item { long item; int buf; int bulk; int b; int f0; int nvalid; int F1; int F2; int64_t L; const float* wave; int64_t row0; };
 
@@ -93,6 +97,13 @@ struct AcousticTileKernel {
   float* boundary;          // [ntiles][2][260]  first / last valid frame magnitudes
 
   AFE_HD long num_items() const { return d.ntiles; }
+  // once per block: the FFT tables move to shared memory (see FbankKernel::block_init)
+  AFE_HD void block_init(unsigned char* smem, int tid) const {
+    float* w = reinterpret_cast<float*>(smem + AcSmem::kHannOff);
+    float* t = reinterpret_cast<float*>(smem + AcSmem::kTwOff);
+    for (int i = tid; i < kRoles * kWinRow; i += kThreads) w[i] = ldg(hann + i);
+    for (int i = tid; i < kRoles * 32; i += kThreads) t[i] = ldg(tw512 + i);
+  }
 
   AFE_HD Item prepare(long item) const {
     Item it;
@@ -159,6 +170,7 @@ struct AcousticTileKernel {
     float* red = reinterpret_cast<float*>(smem + AcSmem::kRedOff);
     float* pf = reinterpret_cast<float*>(smem + AcSmem::kPfOff);       // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
     float* thrs = reinterpret_cast<float*>(smem + AcSmem::kThrOff);    // [0] threshold  [1] total (float)
+    double* dsum = reinterpret_cast<double*>(smem + AcSmem::kDsumOff); // [0] total  [1] sum m k  [2] sum m k^2 (per frame)
     float* sq16 = keep + AcSmem::kSq;  float* zc16 = keep + AcSmem::kZc;  float* lastx = keep + AcSmem::kLast;
     const int role = tid >> 5, f = tid & 31;
     const int kb = role * 16, ke = (role == 15) ? kBins : kb + 16;       // contiguous bin range of this role
@@ -183,7 +195,7 @@ struct AcousticTileKernel {
         }
         if (tid < kGroups16) {
           float s = 0.f, z = 0.f;
-#pragma unroll
+#pragma unroll 4
           for (int j = 0; j < 16; ++j) {
             const int i = 200 + tid * 16 + ((j + tid) & 15);           // rotated: 2-way bank conflicts
             const float a = raw[i], c = raw[i + 1];
@@ -198,8 +210,10 @@ struct AcousticTileKernel {
       case 2: {   // Hann window + stage 1 of the real FFT
         float r[25];
         const float* col = dbuf + (kHop + kHop / 32) * f + role;  // phys_idx(160 f + 16 n1 + role) = 165 f + role + 16 n1 + (n1 >> 1)
-        windowed_column<float>(hann + role * kWinRow, r, [col](int n1) { return col[16 * n1 + (n1 >> 1)]; });
-        rfft512_stage1<float>(r, role, f, tw512, ex);
+        const float* wrow = reinterpret_cast<const float*>(smem + AcSmem::kHannOff) + role * kWinRow;
+        const float* twrow = reinterpret_cast<const float*>(smem + AcSmem::kTwOff) + role * 32;
+        windowed_column_fn<float>([wrow](int n1) { return wrow[n1]; }, r, [col](int n1) { return col[16 * n1 + (n1 >> 1)]; });
+        rfft512_stage1_tw<float, kTileFrames>(r, role, f, [twrow](int k1, float& cc, float& ss) { cc = twrow[2 * k1]; ss = twrow[2 * k1 + 1]; }, ex);
       } break;
       case 3:     // stage 2: power (mel bank) and magnitude (spectral features)
         rfft512_stage2<float, true>(role, f, ex, sP, sM);
@@ -213,8 +227,7 @@ struct AcousticTileKernel {
           mx = tmax(mx, db);
         });
         red[tid] = mx;
-        // moments over k = kb + j with the LOCAL index j as float64 immediates (small integers fit
-        // the 32-bit immediate form): 4 FP64 operations per bin, shifted to k once per thread
+        // moments over k = kb + j with the LOCAL index j (exact small integers), shifted to k once per thread
         double e = 0.0, c = 0.0, c2 = 0.0;
         float fx = 0.f;
         const bool has_next = (f + 1 < it.nvalid);
@@ -222,21 +235,23 @@ struct AcousticTileKernel {
         float* bd = (f == 0) ? boundary + it.item * 2 * kBoundary
                              : (f == it.nvalid - 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
         float* bd2 = (f == 0 && it.nvalid == 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
-#define AFE_AC_BIN(j) {                                                            \
-            const float m = sM[(kb + (j)) * kTileFrames + f];                          \
-            const double md = (double)m;                                               \
-            e += md; c += md * (double)(j); c2 += md * (double)((j) * (j));            \
-            if (has_next) fx += tmax(sM[(kb + (j)) * kTileFrames + f + 1] - m, 0.f);   \
-            if (bd) bd[kb + (j)] = m;                                                  \
-            if (bd2) bd2[kb + (j)] = m; }
-        if (role < 15) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) AFE_AC_BIN(j)
-        } else {
-#pragma unroll
-          for (int j = 0; j < 17; ++j) AFE_AC_BIN(j)
+        // a ROLLED loop: the phase runs once per tile, so its cost on the B200 is the instruction fetch of
+        // cold code -- 17 unrolled copies of this body were slower than the loop-carried FP64 chains
+        {
+          const float* mp = sM + kb * kTileFrames + f;
+          const int nb = ke - kb;
+          double jd = 0.0;
+#pragma unroll 2
+          for (int j = 0; j < nb; ++j) {
+            const float m = mp[j * kTileFrames];
+            const double md = nonneg_to_double(m);
+            e += md; c += md * jd; c2 += md * (jd * jd);
+            if (has_next) fx += tmax(mp[j * kTileFrames + 1] - m, 0.f);
+            if (bd) bd[kb + j] = m;
+            if (bd2) bd2[kb + j] = m;
+            jd += 1.0;
+          }
         }
-#undef AFE_AC_BIN
         {   // sum m k = kb e + c ; sum m k^2 = kb^2 e + 2 kb c + c2   (all exact products)
           const double kd = (double)kb;
           c2 = c2 + kd * (2.0 * c + kd * e);
@@ -244,41 +259,53 @@ struct AcousticTileKernel {
         }
         part[0 * 512 + tid] = e; part[1 * 512 + tid] = c; part[2 * 512 + tid] = c2; fxp[tid] = fx;
       } break;
-      case 5: {   // per-frame scalars: warp 0 spectral totals, warp 1 rms / zcr, warp 2 max dB
+      case 5: {   // per-frame scalars, one 16-step chain per warp: 0 energy prefix, 1 rms / zcr, 2 max dB, 3 / 4 moments, 5 flux
         if (role == 0) {
-          double tot = 0.0, C = 0.0, C2 = 0.0;
-          float fx = 0.f;
-#pragma unroll
+          double tot = 0.0;
+#pragma unroll 4
           for (int r = 0; r < kRoles; ++r) {
             part[3 * 512 + r * 32 + f] = tot;               // exclusive prefix: cum_energy before role r's bins
-            tot += part[0 * 512 + r * 32 + f]; C += part[1 * 512 + r * 32 + f]; C2 += part[2 * 512 + r * 32 + f];
-            fx += fxp[r * 32 + f];
+            tot += part[0 * 512 + r * 32 + f];
           }
           const float total = (float)tot;                  // cum_energy[-1] (float64 accumulate like ATen's cumsum)
-          const float energy = total + 1e-8f;
+          dsum[f] = tot;
+          thrs[f] = 0.85f * (total + 1e-8f);
+          thrs[32 + f] = total;
+        } else if (role == 1) {
+          float s = 0.f, z = 0.f;
+#pragma unroll 5
+          for (int g = 0; g < 25; ++g) { s += sq16[10 * f + g]; z += zc16[10 * f + g]; }
+          pf[4 * 32 + f] = fast_sqrt(s / 400.f);
+          pf[5 * 32 + f] = (z - lastx[f]) / 400.f;
+        } else if (role == 2) {
+          float mx = -3.0e38f;
+#pragma unroll 4
+          for (int r = 0; r < kRoles; ++r) mx = tmax(mx, red[r * 32 + f]);
+          pf[6 * 32 + f] = mx;
+        } else if (role == 3 || role == 4) {
+          const double* src = part + (role - 2) * 512 + f;  // role 3: sum m k, role 4: sum m k^2
+          double acc = 0.0;
+#pragma unroll 4
+          for (int r = 0; r < kRoles; ++r) acc += src[r * 32];
+          dsum[(role - 2) * 32 + f] = acc;
+        } else if (role == 5) {
+          float fx = 0.f;
+#pragma unroll 4
+          for (int r = 0; r < kRoles; ++r) fx += fxp[r * 32 + f];
+          pf[3 * 32 + f] = fx;
+        }
+      } break;
+      case 6: {   // rolloff: only the role whose bin range holds the 85 % crossing scans its bins
+        if (role == 0) {   // centroid and bandwidth from the three moments
+          const double tot = dsum[f], C = dsum[32 + f], C2 = dsum[64 + f];
+          const float energy = thrs[32 + f] + 1e-8f;
           const float cen = 31.25f * (float)C / energy;
           // sum m (31.25 k - cen)^2 from the three moments, in float64
           const double cd = (double)cen;
           const double num = (31.25 * 31.25) * C2 - 2.0 * 31.25 * cd * C + cd * cd * tot;
           pf[0 * 32 + f] = cen;
           pf[1 * 32 + f] = fast_sqrt((float)(num > 0.0 ? num : 0.0) / energy);
-          pf[3 * 32 + f] = fx;
-          thrs[f] = 0.85f * (total + 1e-8f);
-          thrs[32 + f] = total;
-        } else if (role == 1) {
-          float s = 0.f, z = 0.f;
-#pragma unroll
-          for (int g = 0; g < 25; ++g) { s += sq16[10 * f + g]; z += zc16[10 * f + g]; }
-          pf[4 * 32 + f] = fast_sqrt(s / 400.f);
-          pf[5 * 32 + f] = (z - lastx[f]) / 400.f;
-        } else if (role == 2) {
-          float mx = -3.0e38f;
-#pragma unroll
-          for (int r = 0; r < kRoles; ++r) mx = tmax(mx, red[r * 32 + f]);
-          pf[6 * 32 + f] = mx;
         }
-      } break;
-      case 6: {   // rolloff: only the role whose bin range holds the 85 % crossing scans its bins
         const float thr = thrs[f];
         const double lo = part[3 * 512 + tid];
         const double hi = lo + part[0 * 512 + tid];         // == the next role's prefix (same additions)
@@ -287,47 +314,56 @@ struct AcousticTileKernel {
         if (role == 15 && hi_below) {
           pf[2 * 32 + f] = 0.f;                             // no bin reaches the threshold: argmax of all-False is 0
         } else if (lo_below && !hi_below) {
-          // cum is monotone, so the number of bins below the threshold is a plain count:
-          // straight-line code, the only dependent chain is the 16 additions
+          // cum is monotone, so the number of bins below the threshold is a plain count; the only
+          // dependent chain is the 16 additions (rolled loop: cold code, see phase 4)
           double acc = lo;
           int below = 0;
-          if (role < 15) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              acc += (double)sM[(kb + j) * kTileFrames + f];
-              below += ((float)acc < thr) ? 1 : 0;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 17; ++j) {
-              acc += (double)sM[(kb + j) * kTileFrames + f];
-              below += ((float)acc < thr) ? 1 : 0;
-            }
+          const float* mp = sM + kb * kTileFrames + f;
+          const int nb = ke - kb;
+#pragma unroll 1
+          for (int j = 0; j < nb; ++j) {
+            acc += nonneg_to_double(mp[j * kTileFrames]);
+            below += ((float)acc < thr) ? 1 : 0;
           }
           pf[2 * 32 + f] = 31.25f * (float)(kb + below);
         }
       } break;
-      case 7: {   // tile record, boundary spectra, mel-dB rows
+      case 7: {   // tile record (one warp per statistic, lane = frame, fixed-tree reductions), mel-dB rows
         double* rec = tile_rec + it.item * kTileRec;
-        if (tid < 5) {          // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff
-          const int src = (tid == 0) ? 4 : (tid == 1) ? 5 : (tid - 2);
-          const int n = (tid < 2) ? tmax(0, tmin(kTileFrames, it.F1 - it.f0)) : it.nvalid;
-          double s, ss;
-          stat32(pf + src * 32, n, s, ss);
-          rec[2 * tid] = s; rec[2 * tid + 1] = ss;
-        } else if (tid == 32) {  // rms range
-          const int n = tmax(0, tmin(kTileFrames, it.F1 - it.f0));
-          double mn = 3.0e38, mxv = -3.0e38;
-          for (int j = 0; j < n; ++j) { const double v = (double)pf[4 * 32 + j]; mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv; }
-          rec[11] = mn; rec[12] = mxv;
-        } else if (tid == 64) {
-          double s = 0.0;
-          for (int j = 0; j + 1 < it.nvalid; ++j) { const double v = (double)pf[3 * 32 + j]; s += v * v; }
-          rec[10] = s;
-        } else if (tid == 96) {
-          float mx = -3.0e38f;
-          for (int j = 0; j < it.nvalid; ++j) mx = tmax(mx, pf[6 * 32 + j]);
-          rec[13] = (double)mx;
+        if (role < 8) {
+          // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff: (sum, sum sq); 5 flux energy; 6 rms range; 7 max dB
+          const int n1 = tmax(0, tmin(kTileFrames, it.F1 - it.f0));
+          const int src = (role == 0) ? 4 : (role == 1) ? 5 : (role < 5) ? (role - 2) : (role == 5) ? 3 : (role == 6) ? 4 : 6;
+          const int n = (role < 2 || role == 6) ? n1 : (role == 5) ? it.nvalid - 1 : it.nvalid;
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+          const double v = (double)pf[src * 32 + f];
+          if (role < 6) {
+            const double x = (f < n) ? v : 0.0;
+            const double s = warp_tree_sum(x), ss = warp_tree_sum(x * x);
+            if (f == 0) {
+              if (role < 5) { rec[2 * role] = s; rec[2 * role + 1] = ss; } else rec[10] = ss;
+            }
+          } else if (role == 6) {
+            const double mn = warp_tree_min((f < n) ? v : 3.0e38), mxv = warp_tree_max((f < n) ? v : -3.0e38);
+            if (f == 0) { rec[11] = mn; rec[12] = mxv; }
+          } else {
+            const double mxv = warp_tree_max((f < n) ? v : -3.0e38);
+            if (f == 0) rec[13] = (double)(float)mxv;
+          }
+#else
+          if (f == 0) {   // host emulation: lane 0 walks the same trees
+            double a[32], q[32], mn = 3.0e38, mxv = -3.0e38;
+            for (int j = 0; j < 32; ++j) {
+              const double v = (j < n) ? (double)pf[src * 32 + j] : 0.0;
+              a[j] = v; q[j] = v * v;
+              if (j < n) { mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv; }
+            }
+            if (role < 5) { rec[2 * role] = tree32_sum(a); rec[2 * role + 1] = tree32_sum(q); }
+            else if (role == 5) rec[10] = tree32_sum(q);
+            else if (role == 6) { rec[11] = mn; rec[12] = mxv; }
+            else rec[13] = (double)(float)mxv;
+          }
+#endif
         }
         float* dst = meldb + (it.row0 + it.f0) * kAcMel;
         for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];

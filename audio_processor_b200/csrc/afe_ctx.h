@@ -50,6 +50,8 @@ struct afe_ctx {
   float log_floor = 0.f;
   struct MelDev { const float* up; const float* dn; const int32_t* iv_start; const int32_t* iv_count; const int32_t* role_iv; };
   MelDev kaldi_mel_dev{}, htk_mel_dev{};
+  struct MelIvPtr { const afe::MelIvOp* ops; const int32_t* role_op; };
+  MelIvPtr kaldi_iv{}, htk_iv{};                                 // table-driven banks (afe_mel_loop.h)
   std::mutex mu;
   std::map<std::pair<int, int>, afe::DeviceTaps> taps;          // (orig, new) -> bank
   std::vector<afe::StagingBlock> staging;

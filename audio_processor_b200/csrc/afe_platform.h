@@ -126,6 +126,46 @@ AFE_HD void ldg2(const float* p, float& a, float& b) {
   a = v.x; b = v.y;
 }
 
+// exact float -> double of a value that is >= 0 (magnitudes, powers): three integer instructions instead of
+// the quarter-rate F2F conversion (8.5+ cycles of the XU pipe per warp instruction on the B200).
+// Zero, infinity and NaN map like the cast; denormals do not occur (producers flush them).
+AFE_HD double nonneg_to_double(float x) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  const unsigned b = __float_as_uint(x);
+  unsigned hi = (b >> 3) + 0x38000000u;                  // exponent rebias 127 -> 1023, top 20 mantissa bits
+  hi = (b >= 0x7f800000u) ? (hi | 0x7ff00000u) : hi;     // inf / NaN keep an all-ones exponent
+  hi = b ? hi : 0u;
+  return __hiloint2double((int)hi, (int)(b << 29));
+#else
+  return (double)x;
+#endif
+}
+
+// sum / min / max over the 32 lanes of a warp as the fixed binary tree ((v0+v1)+(v2+v3))+...; every lane
+// gets the result.  tree32_* are the host-emulation twins over an array of the 32 lane values.
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+__device__ __forceinline__ double warp_tree_sum(double v) {
+#pragma unroll
+  for (int w = 1; w < 32; w <<= 1) v += __shfl_xor_sync(0xffffffffu, v, w);
+  return v;
+}
+__device__ __forceinline__ double warp_tree_min(double v) {
+#pragma unroll
+  for (int w = 1; w < 32; w <<= 1) { const double o = __shfl_xor_sync(0xffffffffu, v, w); v = o < v ? o : v; }
+  return v;
+}
+__device__ __forceinline__ double warp_tree_max(double v) {
+#pragma unroll
+  for (int w = 1; w < 32; w <<= 1) { const double o = __shfl_xor_sync(0xffffffffu, v, w); v = o > v ? o : v; }
+  return v;
+}
+#endif
+AFE_HD double tree32_sum(double (&a)[32]) {
+  for (int w = 1; w < 32; w <<= 1)
+    for (int i = 0; i < 32; i += 2 * w) a[i] = a[i] + a[i + w];
+  return a[0];
+}
+
 // a value every lane of the warp holds (e.g. the warp's role): broadcasting it from lane 0 tells the
 // compiler so, and loads indexed by it from the kernel parameters become uniform constant loads
 AFE_HD int warp_uniform(int v) {
@@ -244,7 +284,7 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
     }
     __syncthreads();
     uint32_t parbits = 0u;                 // bit b = phase parity of staging buffer b's mbarrier
-    long long tacc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // kTrace: cycles per phase (registers)
+    long long tacc[24] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // kTrace: [0..7] own work, [8..15] work + barrier wait, [16] items
     for (int it = 0; item < end; ++item, ++it) {
       const int buf = it & 1;
       long long t0 = 0, tp = 0;
@@ -265,7 +305,7 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
       }
       if (cur.bulk) { mbar_wait(&bars[buf], (parbits >> buf) & 1u); parbits ^= 1u << buf; }
       else { k.phase(0, cur, afe_smem, tid); __syncthreads(); }
-      if constexpr (kTrace) { t0 = clock64(); tacc[0] += t0 - tp; tacc[15] += 1; }
+      if constexpr (kTrace) { t0 = clock64(); tacc[0] += t0 - tp; tacc[16] += 1; }
 #pragma unroll
       for (int ph = 1; ph < K::kPhases; ++ph) {
         k.phase(ph, cur, afe_smem, tid);
@@ -279,13 +319,13 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
           for (int ph = K::kPhases; ph < K::kPhases + K::kTailPhases; ++ph) {
             k.phase(ph, cur, afe_smem, tid);
             __syncthreads();
-            if constexpr (kTrace) { const long long t1 = clock64(); tacc[7] += t1 - t0; t0 = t1; }
+            if constexpr (kTrace) { const long long t1 = clock64(); tacc[7] += t1 - t0; tacc[15] += t1 - t0; t0 = t1; }
           }
         }
       }
     }
     if constexpr (kTrace) {     // lane 0 of every warp: trace[(block * 32 + warp) * 16 + slot]
-      if ((tid & 31) == 0) for (int i = 0; i < 16; ++i) trace[((size_t)blockIdx.x * 32 + (tid >> 5)) * 16 + i] = (unsigned long long)tacc[i];
+      if ((tid & 31) == 0) for (int i = 0; i < 24; ++i) trace[((size_t)blockIdx.x * 32 + (tid >> 5)) * 24 + i] = (unsigned long long)tacc[i];
     }
   } else {
     for (long item = blockIdx.x; item < n; item += gridDim.x) {
@@ -327,7 +367,7 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t strea
       cudaFuncSetAttribute(tfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
       cudaFuncSetAttribute(tfn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
       unsigned long long* tr = nullptr;
-      const size_t nslots = (size_t)grid * 32 * 16;
+      const size_t nslots = (size_t)grid * 32 * 24;
       cudaMallocManaged(&tr, sizeof(unsigned long long) * nslots);
       std::memset(tr, 0, sizeof(unsigned long long) * nslots);
       phased_kernel<K, true><<<(unsigned)grid, K::kThreads, smem_bytes, stream>>>(k, tr);
@@ -336,13 +376,13 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t strea
       const int nw = K::kThreads / 32;
       double wmin[8] = {0}, wmean[8] = {0}, wmax[8] = {0}, wall[8] = {0}, items = 0;
       for (long b = 0; b < grid; ++b) {
-        const double it_b = (double)tr[(size_t)b * 32 * 16 + 15];
+        const double it_b = (double)tr[(size_t)b * 32 * 24 + 16];
         items += it_b;
         for (int p = 0; p < 8; ++p) {
           double mn = 1e30, mx = 0, sm = 0;
-          for (int w = 0; w < nw; ++w) { const double v = (double)tr[((size_t)b * 32 + w) * 16 + p]; mn = v < mn ? v : mn; mx = v > mx ? v : mx; sm += v; }
+          for (int w = 0; w < nw; ++w) { const double v = (double)tr[((size_t)b * 32 + w) * 24 + p]; mn = v < mn ? v : mn; mx = v > mx ? v : mx; sm += v; }
           wmin[p] += mn; wmax[p] += mx; wmean[p] += sm / nw;
-          wall[p] += (double)tr[((size_t)b * 32) * 16 + 8 + p];
+          wall[p] += (double)tr[((size_t)b * 32) * 24 + 8 + p];
         }
       }
       std::fprintf(stderr, "[afe trace] %s: %ld blocks, %.0f items; cycles per item, phase: warp work min/mean/max -> wall\n", __PRETTY_FUNCTION__, grid, items);
@@ -350,7 +390,7 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t strea
       std::fprintf(stderr, "[afe trace]   prologue+wait %.0f/%.0f/%.0f\n", wmin[0] / items, wmean[0] / items, wmax[0] / items);
       for (int p = 1; p < 8; ++p) {
         if (wall[p] == 0) continue;
-        std::fprintf(stderr, "[afe trace]   phase %d%s: %.0f/%.0f/%.0f -> %.0f\n", p, p == 7 ? " (tail)" : "", wmin[p] / items, wmean[p] / items, wmax[p] / items, wall[p] / items);
+        std::fprintf(stderr, "[afe trace]   phase %d%s: %.0f/%.0f/%.0f -> %.0f\n", p, (p == 7 && K::kTailPhases > 0) ? " (tail)" : "", wmin[p] / items, wmean[p] / items, wmax[p] / items, wall[p] / items);
         tot += wall[p] / items;
       }
       std::fprintf(stderr, "[afe trace]   total %.0f\n", tot);

@@ -243,6 +243,7 @@ int afe_create(int device, afe_ctx** out) {
     ok = ok && (c->kaldi_mel_dev.up = c->upload(mel.up)) && (c->kaldi_mel_dev.dn = c->upload(mel.dn)) &&
          (c->kaldi_mel_dev.iv_start = c->upload(mel.iv_start)) && (c->kaldi_mel_dev.iv_count = c->upload(mel.iv_count)) &&
          (c->kaldi_mel_dev.role_iv = c->upload(mel.role_iv));
+    { const MelIvOps mo = make_mel_iv_ops(mel); ok = ok && (c->kaldi_iv.ops = c->upload(mo.ops)) && (c->kaldi_iv.role_op = c->upload(mo.role_op)); }
     std::vector<double> hn = make_hann_periodic();
     std::vector<float> hn32(16 * 26, 0.f);
     for (size_t i = 0; i < hn.size(); ++i) hn32[(i % 16) * 26 + i / 16] = (float)(hn[i] * 0.5);
@@ -253,6 +254,7 @@ int afe_create(int device, afe_ctx** out) {
     ok = ok && (c->htk_mel_dev.up = c->upload(htk.up)) && (c->htk_mel_dev.dn = c->upload(htk.dn)) &&
          (c->htk_mel_dev.iv_start = c->upload(htk.iv_start)) && (c->htk_mel_dev.iv_count = c->upload(htk.iv_count)) &&
          (c->htk_mel_dev.role_iv = c->upload(htk.role_iv));
+    { const MelIvOps mo = make_mel_iv_ops(htk); ok = ok && (c->htk_iv.ops = c->upload(mo.ops)) && (c->htk_iv.role_op = c->upload(mo.role_op)); }
     c->h_dct = make_dct_matrix();
     ok = ok && (c->d_dct = c->upload(c->h_dct));
     c->log_floor = (float)std::log((double)kMelFloor);
