@@ -43,6 +43,15 @@ class AfeError(RuntimeError):
         self.message = message
 
 
+class WavInfo(C.Structure):
+    """``afe_wav_info`` of include/afe.h."""
+    _fields_ = [("format", C.c_int32), ("channels", C.c_int32), ("sample_rate", C.c_int32),
+                ("bits_per_sample", C.c_int32), ("block_align", C.c_int32), ("reserved", C.c_int32),
+                ("data_offset", C.c_int64), ("data_bytes", C.c_int64), ("num_frames", C.c_int64)]
+
+
+WAV_U8, WAV_S16, WAV_S24, WAV_S32, WAV_F32, WAV_F64 = 1, 2, 3, 4, 5, 6
+
 # every symbol include/afe.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "afe_version": (C.c_char_p, []),
@@ -67,6 +76,11 @@ SIGNATURES = {
                                            C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p,
                                            C.c_size_t]),
     "afe_pcm16_to_float": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "afe_wav_parse": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int64, C.c_void_p]),
+    "afe_wav_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p]),
+    "afe_resample_batch_wav16": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
+                                           C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p,
+                                           C.c_size_t]),
     "afe_mix_stereo": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "afe_fbank_layout": (C.c_int, [c_i64p, C.c_int, C.c_int, c_i64p, c_i64p]),
     "afe_fbank_workspace_bytes": (C.c_size_t, [c_i64p, C.c_int]),

@@ -66,6 +66,25 @@ class AudioProcessor:
         self.processor = processor or FbankProcessor(FbankFeatureExtractor(device=self.device))
         self.model = None
 
+    # -------------------------------------------------------------- reference :72-93
+    def load_audio(self, audio_path):
+        """``(waveform float32 (C, L), sample_rate)`` like ``torchaudio.load``; the file's bytes go to the
+        device as they are and are decoded there (wav.py).  ``.ogg`` goes through ffmpeg as in the
+        reference.  Errors propagate (the reference logs and re-raises)."""
+        from . import wav
+        if str(audio_path).lower().endswith(".ogg"):
+            return wav.load_audio(wav.ffmpeg_wav_bytes(audio_path), self.device)
+        return wav.load_audio(audio_path, self.device)
+
+    def load_pcm(self, audio_path):
+        """The fast route for 16-bit wav files: ``(pcm, sample_rate)`` where ``pcm`` is an int16 (C, L) view
+        of the frames in pinned memory; ``split_audio`` / ``CallFrontend.process_calls`` take it in place
+        of the float waveform (2 bytes per sample over PCIe, decode fused into the resampler)."""
+        from . import wav
+        if str(audio_path).lower().endswith(".ogg"):
+            return wav.load_pcm16(wav.ffmpeg_wav_bytes(audio_path))
+        return wav.load_pcm16(audio_path)
+
     # -------------------------------------------------------------- reference :99-102
     @lru_cache(maxsize=100)
     def get_resampler(self, orig_freq: int, new_freq: int) -> Resampler:
@@ -76,6 +95,15 @@ class AudioProcessor:
         fe = self.frontend
         waveform = waveform.to(fe.device, non_blocking=True)
         mixed = None
+        if waveform.dtype == torch.int16 and sample_rate != self.target_sample_rate:
+            # 16-bit PCM from load_pcm: decode fused into the (batched, here one-call) resampler
+            if waveform.shape[0] == 2:
+                (waveform,), (mixed,) = fe.resample_batch([waveform], sample_rate, self.target_sample_rate, want_mixed=True)
+            else:
+                (waveform,) = fe.resample_batch([waveform], sample_rate, self.target_sample_rate)
+            sample_rate = self.target_sample_rate
+        elif waveform.dtype == torch.int16:
+            waveform = fe.to_float(waveform)
         if sample_rate != self.target_sample_rate:
             if waveform.shape[0] == 2:
                 waveform, mixed = fe.resample(waveform, sample_rate, self.target_sample_rate, want_mixed=True)

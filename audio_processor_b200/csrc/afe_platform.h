@@ -37,6 +37,7 @@ struct alignas(8) float2 { float x, y; };
 struct alignas(16) double2 { double x, y; };
 struct alignas(16) float4 { float x, y, z, w; };
 struct alignas(8) short4 { short x, y, z, w; };
+struct alignas(16) int4 { int x, y, z, w; };
 #endif
 
 namespace afe {

@@ -1,4 +1,6 @@
 // afe_resample.cu -- C ABI entry points for resampling and the stereo mix.
+#include <cstring>
+
 #include "afe_ctx.h"
 #include "afe_resample_kernels.h"
 
@@ -38,21 +40,68 @@ struct Pcm16Kernel {
     }
   }
 };
+// torchaudio.load(normalize=True) of an interleaved data chunk -> planar float32 [channels][frames].
+// Byte-wise loads: a data chunk starts wherever the header ends, so nothing is assumed aligned.
+struct WavDecodeKernel {
+  static constexpr int kThreads = 256;
+  static constexpr int kMinBlocks = 8;
+  static constexpr int kPhases = 1;
+  static constexpr int kItem = 2048;                 // frames per item
+  const unsigned char* in; float* out; int64_t frames; int channels; int format;
+  AFE_PLAIN_ITEM
+  AFE_HD long num_items() const { return (long)((frames + kItem - 1) / kItem); }
+  AFE_HD static float sample(const unsigned char* p, int format) {
+    switch (format) {
+      case AFE_WAV_U8:  return (float)((int)p[0] - 128) * (1.0f / 128.0f);
+      case AFE_WAV_S16: return (float)(int16_t)((unsigned)p[0] | ((unsigned)p[1] << 8)) * (1.0f / 32768.0f);
+      case AFE_WAV_S24: {   // sign-extend through the top of an int32, as a decoder that widens to s32 does
+        const int32_t v = (int32_t)(((uint32_t)p[0] << 8) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 24));
+        return (float)v * (1.0f / 2147483648.0f);
+      }
+      case AFE_WAV_S32: {
+        const int32_t v = (int32_t)((uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24));
+        return (float)v * (1.0f / 2147483648.0f);
+      }
+      case AFE_WAV_F32: {
+        const uint32_t u = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+        float f; memcpy(&f, &u, 4); return f;
+      }
+      default: {
+        uint64_t u = 0;
+        for (int i = 7; i >= 0; --i) u = (u << 8) | p[i];
+        double d; memcpy(&d, &u, 8); return (float)d;
+      }
+    }
+  }
+  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+    const int bps = format == AFE_WAV_U8 ? 1 : format == AFE_WAV_S16 ? 2 : format == AFE_WAV_S24 ? 3 : format == AFE_WAV_F64 ? 8 : 4;
+    const int64_t f0 = it.item * kItem;
+    const int nf = (int)tmin<int64_t>(kItem, frames - f0);
+    // consecutive threads take consecutive samples of the interleaved run (coalesced reads);
+    // the planar writes are `channels` coalesced runs
+    const int total = nf * channels;
+    const unsigned char* base = in + f0 * channels * bps;
+    for (int i = tid; i < total; i += kThreads) {
+      const int f = i / channels, c = i - f * channels;
+      out[(int64_t)c * frames + f0 + f] = sample(base + (int64_t)i * bps, format);
+    }
+  }
+};
 }  // namespace afe
 
 namespace {
 // one launch of the 1:2 kernel over `ncalls` calls (device descriptors) or the inline call
 int launch_up2x(afe_ctx* ctx, cudaStream_t s, const ResampleTaps& t, const UpCall* d_calls, const UpCall& one,
-                int ncalls, int rows, bool stereo_mix, long nitems = -1, bool pcm16 = false) {
+                int ncalls, int rows, bool stereo_mix, long nitems = -1, int pcm16 = 0) {
   if (nitems < 0) nitems = (long)((one.L + 1023) / 1024) * (stereo_mix ? 1 : rows);
   if (stereo_mix) {
     Upsample2xKernel<true> k;
-    k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = 2; k.nitems = nitems; k.pcm16 = pcm16 ? 1 : 0;
+    k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = 2; k.nitems = nitems; k.pcm16 = pcm16;
     for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
     return afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * 8, s);
   }
   Upsample2xKernel<false> k;
-  k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = rows; k.nitems = nitems; k.pcm16 = pcm16 ? 1 : 0;
+  k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = rows; k.nitems = nitems; k.pcm16 = pcm16;
   for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
   return afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * 8, s);
 }
@@ -124,25 +173,44 @@ int afe_pcm16_to_float(afe_ctx* ctx, void* stream, const int16_t* d_in, int64_t 
   return AFE_OK;
 }
 
-static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_in, bool pcm16, const int64_t* h_lengths,
+static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_in, int pcm16, const int64_t* h_lengths,
                                int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
                                float* const* h_mixed, void* d_workspace, size_t workspace_bytes);
 
 int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, const int64_t* h_lengths, int ncalls,
                        int rows, int orig_hz, int new_hz, float* const* h_out, float* const* h_mixed,
                        void* d_workspace, size_t workspace_bytes) {
-  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), false, h_lengths, ncalls, rows,
+  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), 0, h_lengths, ncalls, rows,
                              orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
 }
 
 int afe_resample_batch_pcm16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
                              int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
                              float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
-  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), true, h_lengths, ncalls, rows,
+  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), 1, h_lengths, ncalls, rows,
                              orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
 }
 
-static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_in, bool pcm16, const int64_t* h_lengths,
+int afe_resample_batch_wav16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
+                             int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                             float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
+  return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), 2, h_lengths, ncalls, rows,
+                             orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
+}
+
+int afe_wav_decode(afe_ctx* ctx, void* stream, const void* d_frames, int format, int channels, int64_t num_frames,
+                   float* d_out) {
+  if (!ctx || channels <= 0 || num_frames < 0 || format < AFE_WAV_U8 || format > AFE_WAV_F64 ||
+      (num_frames > 0 && (!d_frames || !d_out)))
+    return fail(AFE_ERR_INVALID, "afe_wav_decode: bad arguments");
+  if (num_frames == 0) return AFE_OK;
+  WavDecodeKernel k{static_cast<const unsigned char*>(d_frames), d_out, num_frames, channels, format};
+  ProfScope ps(ctx, AFE_K_MIX, (cudaStream_t)stream);
+  if (afe_launch(k, 0, ctx->num_sms * 8, (cudaStream_t)stream) != 0) return fail(AFE_ERR_CUDA, "afe_wav_decode: launch failed");
+  return AFE_OK;
+}
+
+static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_in, int pcm16, const int64_t* h_lengths,
                                int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
                                float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
   if (!ctx || ncalls < 0 || rows <= 0 || orig_hz <= 0 || new_hz <= 0)

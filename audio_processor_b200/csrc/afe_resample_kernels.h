@@ -38,7 +38,8 @@ template <bool STEREO> struct Upsample2xKernel {
   UpCall one;
   int ncalls;
   int rows;               // rows per call (STEREO: 2)
-  int pcm16;              // inputs are int16 PCM (torchaudio.load's x / 32768 happens while staging)
+  int pcm16;              // 1: inputs are int16 PCM, planar [rows][L]; 2: interleaved frames [L][rows] as in a wav
+                          // file (torchaudio.load's x / 32768 and the de-interleave happen while staging)
   long nitems;
   float h[2][15];
 
@@ -67,8 +68,9 @@ template <bool STEREO> struct Upsample2xKernel {
     const int row0 = STEREO ? 0 : (int)(local / ipr);
     it.n0 = (int64_t)(local % ipr) * kPos;
     it.L = c.L;
-    it.src = pcm16 ? reinterpret_cast<const float*>(reinterpret_cast<const int16_t*>(c.in) + (int64_t)row0 * c.L)
-                   : c.in + (int64_t)row0 * c.L;
+    it.src = pcm16 == 2 ? reinterpret_cast<const float*>(reinterpret_cast<const int16_t*>(c.in) + row0)
+           : pcm16     ? reinterpret_cast<const float*>(reinterpret_cast<const int16_t*>(c.in) + (int64_t)row0 * c.L)
+                       : c.in + (int64_t)row0 * c.L;
     it.dst = c.out + (int64_t)row0 * 2 * c.L;
     it.mix = c.mixed;
     return it;
@@ -77,6 +79,40 @@ template <bool STEREO> struct Upsample2xKernel {
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     float* xs = reinterpret_cast<float*>(smem);
     const int64_t n0 = it.n0, L = it.L;
+    if (ph == 0 && pcm16 == 2) {
+      // frames as they lie in a wav file: sample (g, r) at src[g * rows + r]; it.src already points at row0
+      constexpr float kScale = 1.0f / 32768.0f;
+      const int16_t* src = reinterpret_cast<const int16_t*>(it.src);
+      if (STEREO) {
+        const int16_t* p0 = src + 2 * (n0 - 8);
+        if (n0 >= 8 && n0 - 8 + kTile <= L && (reinterpret_cast<uintptr_t>(p0) & 15u) == 0) {
+          // one 128-bit word = 4 frames; low half of each 32-bit lane is channel 0
+          const int4* s4 = reinterpret_cast<const int4*>(p0);
+          float4* a4 = reinterpret_cast<float4*>(xs);
+          float4* c4 = reinterpret_cast<float4*>(xs + kTile);
+          for (int i = tid; i < kTile / 4; i += kThreads) {
+            const int4 v = s4[i];
+            a4[i] = float4{(float)(int16_t)v.x * kScale, (float)(int16_t)v.y * kScale,
+                           (float)(int16_t)v.z * kScale, (float)(int16_t)v.w * kScale};
+            c4[i] = float4{(float)(v.x >> 16) * kScale, (float)(v.y >> 16) * kScale,
+                           (float)(v.z >> 16) * kScale, (float)(v.w >> 16) * kScale};
+          }
+        } else {
+          for (int i = tid; i < kTile; i += kThreads) {
+            const int64_t g = n0 - 8 + i;
+            const bool in = (g >= 0 && g < L);
+            xs[i] = in ? (float)src[2 * g] * kScale : 0.f;
+            xs[kTile + i] = in ? (float)src[2 * g + 1] * kScale : 0.f;
+          }
+        }
+      } else {
+        for (int i = tid; i < kTile; i += kThreads) {
+          const int64_t g = n0 - 8 + i;
+          xs[i] = (g >= 0 && g < L) ? (float)src[g * rows] * kScale : 0.f;
+        }
+      }
+      return;
+    }
     if (ph == 0 && pcm16) {
       constexpr float kScale = 1.0f / 32768.0f;            // exact: the same value as x / 32768
 #pragma unroll

@@ -98,7 +98,9 @@ class CallFrontend:
                 if not c.is_cuda:
                     if c.dtype not in (torch.float32, torch.int16):
                         raise TypeError("process_calls: calls must be float32 waveforms or int16 PCM")
-                    xdev[i] = xin[offs[i]:offs[i] + c.numel() * c.element_size()].view(c.dtype).view(c.shape)
+                    flat = xin[offs[i]:offs[i] + c.numel() * c.element_size()].view(c.dtype)
+                    # wav frames keep their interleaved layout: a (C, L) view with strides (1, C)
+                    xdev[i] = flat.view(c.shape[1], c.shape[0]).t() if fe.pcm_kind(c) == "wav" else flat.view(c.shape)
             self._copy_stream.wait_stream(main)
 
         # every host call is enqueued on the copy stream right away, one event per call; device calls
@@ -111,7 +113,10 @@ class CallFrontend:
                     if xdev[i] is None:
                         xs_all[i] = c.to(dev)
                     else:
-                        xdev[i].copy_(c, non_blocking=True)
+                        if fe.pcm_kind(c) == "wav":
+                            xdev[i].t().copy_(c.t(), non_blocking=True)      # both sides contiguous (L, C)
+                        else:
+                            xdev[i].copy_(c, non_blocking=True)
                         xs_all[i] = xdev[i]
                         evs[i] = torch.cuda.Event()
                         evs[i].record(self._copy_stream)
@@ -154,7 +159,7 @@ class CallFrontend:
                     else:
                         ys = fe.resample_batch(grp, sample_rate, sr_t); ms = ys
                 else:
-                    ys = [fe.pcm16_to_float(x) if x.dtype == torch.int16 else x.contiguous() for x in grp]
+                    ys = [fe.to_float(x) for x in grp]
                     ms = [fe.mix_stereo(y) for y in ys] if want_rows == 2 else ys
                 for i, y, m in zip(ids, ys, ms):
                     res.waveforms[i] = (y, m)

@@ -134,10 +134,16 @@ class Frontend:
         n = len(calls)
         if n == 0:
             return ([], []) if want_mixed else []
-        pcm16 = all(c.dtype == torch.int16 for c in calls)     # 16-bit PCM: x / 32768 while staging
-        if pcm16 and self.resampled_length(1000, orig, new) != 2000:
-            calls = [self.pcm16_to_float(c) for c in calls]; pcm16 = False
-        xs = [c.to(device=self.device, dtype=torch.int16 if pcm16 else torch.float32).contiguous() for c in calls]
+        # 16-bit PCM (planar, or interleaved frames as in a wav file): x / 32768 while staging
+        kinds = {self.pcm_kind(c) for c in calls}
+        if kinds != {"f32"} and (len(kinds) > 1 or self.resampled_length(1000, orig, new) != 2000):
+            calls = [self.to_float(c) for c in calls]; kinds = {"f32"}
+        kind = next(iter(kinds))
+        pcm16 = kind != "f32"
+        if kind == "wav":                                       # keep the (1, C) strides of the frames
+            xs = [c.to(device=self.device) for c in calls]
+        else:
+            xs = [c.to(device=self.device, dtype=torch.int16 if pcm16 else torch.float32).contiguous() for c in calls]
         rows = int(xs[0].shape[0])
         if any(x.dim() != 2 or int(x.shape[0]) != rows for x in xs):
             raise ValueError("resample_batch: every call must be (rows, L) with the same number of rows")
@@ -158,7 +164,8 @@ class Frontend:
                 m = buf[o + rows * pad:o + rows * pad + lo].view(1, lo)
                 mixes.append(m); p_mix.append(m.data_ptr())
         ws = self._workspace3(int(self.lib.afe_resample_batch_workspace_bytes(n)))
-        fn = self.lib.afe_resample_batch_pcm16 if pcm16 else self.lib.afe_resample_batch
+        fn = {"f32": self.lib.afe_resample_batch, "pcm": self.lib.afe_resample_batch_pcm16,
+              "wav": self.lib.afe_resample_batch_wav16}[kind]
         with torch.cuda.device(self.device):
             self.lib.check(fn(
                 self.ctx, self._stream(), _native.ptr_array([x.data_ptr() for x in xs]), _native.i64_array(lens), n,
@@ -166,6 +173,38 @@ class Frontend:
                 C.c_void_p(ws.data_ptr()), ws.numel()))
         self._tls.keep_rs = xs                      # inputs stay alive until the next call on this thread
         return (outs, mixes) if want_mixed else outs
+
+    @staticmethod
+    def pcm_kind(x: torch.Tensor) -> str:
+        """"f32": a float waveform; "pcm": int16 planar (C, L); "wav": an int16 (C, L) VIEW of the
+        interleaved frames of a wav data chunk (strides (1, C)), as ``wav.load_pcm16`` returns."""
+        if x.dtype != torch.int16:
+            return "f32"
+        if x.dim() == 2 and int(x.shape[0]) > 1 and tuple(x.stride()) == (1, int(x.shape[0])):
+            return "wav"
+        return "pcm"
+
+    def to_float(self, x: torch.Tensor) -> torch.Tensor:
+        """What ``torchaudio.load`` would have returned for this call: float32 (C, L) on the device."""
+        kind = self.pcm_kind(x)
+        if kind == "pcm":
+            return self.pcm16_to_float(x)
+        if kind == "wav":
+            return self.wav_decode(x.to(self.device).t(), _native.WAV_S16, int(x.shape[0]), int(x.shape[1]))
+        return x.to(device=self.device, dtype=torch.float32).contiguous()
+
+    def wav_decode(self, frames: torch.Tensor, fmt: int, channels: int, num_frames: int) -> torch.Tensor:
+        """Interleaved frames of a wav data chunk (any dtype, contiguous, on the device) ->
+        ``torchaudio.load``'s (channels, num_frames) float32 waveform."""
+        frames = frames.to(self.device)
+        if not frames.is_contiguous():
+            raise ValueError("wav_decode: frames must be the contiguous bytes of the data chunk")
+        out = torch.empty((channels, num_frames), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self.lib.check(self.lib.afe_wav_decode(self.ctx, self._stream(), C.c_void_p(frames.data_ptr()), int(fmt),
+                                                   int(channels), int(num_frames), C.c_void_p(out.data_ptr())))
+        self._tls.keep_wav = frames
+        return out
 
     def pcm16_to_float(self, x: torch.Tensor) -> torch.Tensor:
         """int16 PCM -> float32 in [-1, 1): ``x / 32768`` (torchaudio.load's normalisation)."""

@@ -113,3 +113,18 @@ def cfg3_segments(n_segments: int = 4096, seed: int = 7, kind: str = "speech_lik
 def cfg5_longform(seconds: float = 3600.0, kind: str = "speech_like") -> Tuple[torch.Tensor, int]:
     """cfg5: one mono 44.1 kHz long-form waveform, seed 5."""
     return make_call(seconds, 44100, 5, 1, kind), 44100
+
+
+def wav_image(call: torch.Tensor, sample_rate: int) -> torch.Tensor:
+    """The bytes of a canonical 16-bit PCM wav file holding ``call`` ((C, L) float32 in [-1, 1)): a 44-byte
+    RIFF header followed by the interleaved frames, as a uint8 tensor."""
+    import struct
+    pcm = (call * 32768.0).round().clamp(-32768, 32767).to(torch.int16).t().contiguous()     # (L, C)
+    channels, nbytes = int(call.shape[0]), int(pcm.numel()) * 2
+    head = (b"RIFF" + struct.pack("<I", 36 + nbytes) + b"WAVEfmt " +
+            struct.pack("<IHHIIHH", 16, 1, channels, sample_rate, sample_rate * channels * 2, channels * 2, 16) +
+            b"data" + struct.pack("<I", nbytes))
+    out = torch.empty((44 + nbytes,), dtype=torch.uint8)
+    out[:44] = torch.frombuffer(bytearray(head), dtype=torch.uint8)
+    out[44:] = pcm.view(-1).view(torch.uint8)
+    return out

@@ -101,6 +101,50 @@ int afe_resample_batch_pcm16(afe_ctx* ctx, void* stream, const int16_t* const* h
 /* float32 = int16 / 32768 for `count` samples (other rate pairs, or no resampling at all) */
 int afe_pcm16_to_float(afe_ctx* ctx, void* stream, const int16_t* d_in, int64_t count, float* d_out);
 
+/* ---- audio decode + staging ------------------------------------------ */
+/* Sample encodings of a RIFF/WAVE data chunk (little endian, frames interleaved by channel). */
+typedef enum afe_wav_format {
+  AFE_WAV_U8 = 1, AFE_WAV_S16 = 2, AFE_WAV_S24 = 3, AFE_WAV_S32 = 4, AFE_WAV_F32 = 5, AFE_WAV_F64 = 6
+} afe_wav_format;
+
+typedef struct afe_wav_info {
+  int32_t format;           /* afe_wav_format */
+  int32_t channels;
+  int32_t sample_rate;
+  int32_t bits_per_sample;
+  int32_t block_align;      /* bytes per frame */
+  int32_t reserved;
+  int64_t data_offset;      /* byte offset of the first frame */
+  int64_t data_bytes;       /* bytes of frames present (clamped to the file, whole frames only) */
+  int64_t num_frames;
+} afe_wav_info;
+
+/* Header walk of a RIFF/WAVE file (host only, integers only): what torchaudio.info reports to
+ * AudioFileScanner._validate_file (services/pipeline.py:84-108) and what torchaudio.load needs
+ * to find the samples (AudioProcessor.load_audio, services/audio_processor.py:72-93).  `bytes`
+ * holds the first `nbytes` of a file that is `total_bytes` long (total_bytes >= nbytes; a
+ * header-only read passes the file size).  PCM 8/16/24/32-bit, IEEE float 32/64,
+ * WAVE_FORMAT_EXTENSIBLE; chunks before "data" (LIST, fact, ...) are skipped; a data size of
+ * 0 or 0xFFFFFFFF (ffmpeg writing to a pipe -- the reference's .ogg path) means "to the end".
+ * AFE_ERR_INVALID: not RIFF/WAVE, or the header does not end within nbytes;
+ * AFE_ERR_UNSUPPORTED: a compressed format tag. */
+int afe_wav_parse(const void* bytes, size_t nbytes, int64_t total_bytes, afe_wav_info* out);
+
+/* torchaudio.load's (waveform [channels, frames] float32 in [-1, 1), normalize=True) from the
+ * interleaved frames of a data chunk that already lie in device memory: u8 -> (x-128)/128,
+ * s16 -> x/32768, s24 -> x/2^23, s32 -> float(x)/2^31, f32 -> x, f64 -> float(x).
+ * d_frames needs no alignment beyond 1 byte. */
+int afe_wav_decode(afe_ctx* ctx, void* stream, const void* d_frames, int format, int channels,
+                   int64_t num_frames, float* d_out /*[channels][num_frames]*/);
+
+/* afe_resample_batch_pcm16 reading the frames as they lie in a 16-bit wav file: h_in[c] is a
+ * DEVICE pointer to h_lengths[c] interleaved frames of `rows` int16 samples (L0 R0 L1 R1 ...).
+ * De-interleaving, x / 32768, the 1:2 resampling and the stereo mean happen in one pass: the
+ * 8 kHz float32 waveform of load_audio is never materialised.  Only the 1:2 rate pair. */
+int afe_resample_batch_wav16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
+                             int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
+                             float* const* h_mixed, void* d_workspace, size_t workspace_bytes);
+
 /* mixed = (row0 + row1) * 0.5 for waveforms that need no resampling (split_audio :123-131) */
 int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed);
 

@@ -34,15 +34,42 @@ def resample(x, orig, new, want_mixed=False):
     return (out, mixed) if want_mixed else out
 
 
-def resample_batch(calls, orig, new, want_mixed=False, pcm16=False):
+def wav_parse(data: bytes, total_bytes=None):
+    lib, _ = emu()
+    info = _native.WavInfo()
+    buf = C.create_string_buffer(data, len(data))
+    code = lib.afe_wav_parse(C.cast(buf, C.c_void_p), len(data), len(data) if total_bytes is None else total_bytes,
+                             C.byref(info))
+    if code != 0:
+        return code, lib.afe_last_error().decode()
+    return 0, {k: int(getattr(info, k)) for k, _ in _native.WavInfo._fields_ if k != "reserved"}
+
+
+def wav_decode(frames: bytes, fmt: int, channels: int, misalign: int = 0):
+    """afe_wav_decode on the bytes of a data chunk placed `misalign` bytes off an aligned address."""
     lib, ctx = emu()
-    calls = [np.ascontiguousarray(c, np.int16 if pcm16 else np.float32) for c in calls]
+    bps = {1: 1, 2: 2, 3: 3, 4: 4, 5: 4, 6: 8}[fmt]
+    n = len(frames) // (bps * channels)
+    buf = np.zeros(len(frames) + misalign + 16, np.uint8)
+    buf[misalign:misalign + len(frames)] = np.frombuffer(frames, np.uint8)
+    out = np.full((channels, n), np.float32(-9.0), np.float32)
+    lib.check(lib.afe_wav_decode(ctx, None, C.c_void_p(buf.ctypes.data + misalign), fmt, channels, n, _p(out)))
+    return out
+
+
+def resample_batch(calls, orig, new, want_mixed=False, pcm16=False, wav=False):
+    """``wav``: the calls are int16 (rows, L) arrays handed over as interleaved frames [L][rows]."""
+    lib, ctx = emu()
     n, rows = len(calls), calls[0].shape[0]
     lens = [c.shape[1] for c in calls]
+    if wav:
+        calls = [np.ascontiguousarray(np.asarray(c, np.int16).T) for c in calls]
+    else:
+        calls = [np.ascontiguousarray(c, np.int16 if pcm16 else np.float32) for c in calls]
     outs = [np.full((rows, lib.afe_resampled_length(L, orig, new)), np.float32(-9.0), np.float32) for L in lens]
     mixes = [np.full((1, o.shape[1]), np.float32(-9.0), np.float32) for o in outs] if want_mixed else None
     ws = np.zeros(lib.afe_resample_batch_workspace_bytes(n), np.uint8)
-    fn = lib.afe_resample_batch_pcm16 if pcm16 else lib.afe_resample_batch
+    fn = lib.afe_resample_batch_wav16 if wav else lib.afe_resample_batch_pcm16 if pcm16 else lib.afe_resample_batch
     lib.check(fn(ctx, None, _native.ptr_array([c.ctypes.data for c in calls]),
                                      _native.i64_array(lens), n, rows, orig, new,
                                      _native.ptr_array([o.ctypes.data for o in outs]),
