@@ -90,6 +90,9 @@ SIGNATURES = {
                                          C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "afe_acoustic_batch_placed": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
                                             c_i32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "afe_acoustic_batch_scaled": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
+                                            c_i32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                            C.c_void_p, C.c_size_t]),
     "afe_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "afe_profile_reset": (C.c_int, [C.c_void_p]),
     "afe_profile_read": (C.c_int, [C.c_void_p, c_f64p, c_i64p]),

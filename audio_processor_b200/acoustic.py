@@ -86,3 +86,93 @@ class AcousticFeatureExtractor:
         """Feature lists in the reference's order with zero rows for failures (:736-748)."""
         feats = extract_acoustic_features_batch(list(waveforms), sample_rate, self.device)
         return [list((f if f is not None else zero_features()).values()) for f in feats]
+
+
+_EMPTY_RESULT = {"prediction": "", "confidence": 0.0, "probabilities": []}
+
+
+class AcousticSentimentAnalyzer(AcousticFeatureExtractor):
+    """The acoustic classifier glue of the reference's class of the same name
+    (``analyze_batch_sentiment``, services/sentiment_analysis.py:696-805): all valid waveforms of a batch are
+    featurised in one launch sequence, the ``StandardScaler`` step runs as an epilogue of the last kernel
+    (float64, the operations of ``scaler.transform``), ONE (B, n_features) matrix comes back to the host and
+    goes straight into the sklearn model's ``predict`` / ``predict_proba`` (SVM / RandomForest stay sklearn).
+
+    The fitted models are handed in (the reference loads them with joblib): ``agent_acoustic_model`` /
+    ``agent_acoustic_scaler`` / ``agent_acoustic_id2label`` and the ``client_*`` twins."""
+
+    def __init__(self, device=None, agent_acoustic_model=None, agent_acoustic_scaler=None, agent_acoustic_id2label=None,
+                 client_acoustic_model=None, client_acoustic_scaler=None, client_acoustic_id2label=None, logger=None):
+        super().__init__(device)
+        self.agent_acoustic_model, self.agent_acoustic_scaler = agent_acoustic_model, agent_acoustic_scaler
+        self.client_acoustic_model, self.client_acoustic_scaler = client_acoustic_model, client_acoustic_scaler
+        self.agent_acoustic_id2label, self.client_acoustic_id2label = agent_acoustic_id2label, client_acoustic_id2label
+        self.models_available = all(m is not None for m in (agent_acoustic_model, agent_acoustic_scaler,
+                                                            client_acoustic_model, client_acoustic_scaler))
+        import logging
+        self.logger = logger or logging.getLogger(__name__)
+        self._scalers = {}
+
+    @classmethod
+    def from_reference(cls, analyzer, device=None) -> "AcousticSentimentAnalyzer":
+        """Take the fitted models of a constructed reference analyzer."""
+        names = ("agent_acoustic_model", "agent_acoustic_scaler", "agent_acoustic_id2label",
+                 "client_acoustic_model", "client_acoustic_scaler", "client_acoustic_id2label")
+        return cls(device, **{n: getattr(analyzer, n, None) for n in names}, logger=getattr(analyzer, "logger", None))
+
+    def _scaler_vectors(self, scaler):
+        """(mean, scale) float64 device vectors of ``scaler.n_features_in_`` entries (``with_mean`` /
+        ``with_std`` = False become 0 / 1), cached per scaler object."""
+        import numpy as np
+        key = id(scaler)
+        hit = self._scalers.get(key)
+        if hit is None or hit[0] is not scaler:
+            n = int(scaler.n_features_in_)
+            mean = getattr(scaler, "mean_", None) if getattr(scaler, "with_mean", True) else None
+            scale = getattr(scaler, "scale_", None) if getattr(scaler, "with_std", True) else None
+            mean = np.zeros(n) if mean is None else np.asarray(mean, np.float64)
+            scale = np.ones(n) if scale is None else np.asarray(scale, np.float64)
+            fe = runtime.get_frontend(self.device)
+            hit = (scaler, torch.from_numpy(mean.copy()).to(fe.device), torch.from_numpy(scale.copy()).to(fe.device))
+            self._scalers[key] = hit
+        return hit[1], hit[2]
+
+    def _scaled_features(self, waveforms: Sequence[torch.Tensor], sample_rate: int, scaler):
+        """``acoustic_scaler.transform(feature_lists)`` of :736-752 as a float64 numpy matrix."""
+        fe = runtime.get_frontend(self.device)
+        dev_waves, lens = fe._to_device_1d([w.reshape(-1) for w in waveforms])
+        _, _, scaled = fe.acoustic_ptrs([t.data_ptr() if t.numel() else 0 for t in dev_waves], lens, sample_rate,
+                                        scaler=self._scaler_vectors(scaler))
+        return scaled.cpu().numpy()
+
+    def analyze_batch_sentiment(self, waveforms: List[torch.Tensor], sample_rate: int, speaker: str):
+        import numpy as np
+        empty = lambda: dict(_EMPTY_RESULT, probabilities=[])          # noqa: E731
+        try:
+            if not waveforms:
+                return []
+            if not getattr(self, "models_available", False):
+                return [empty() for _ in waveforms]
+            valid = [i for i, w in enumerate(waveforms) if w is not None and w.numel() > 0]
+            if not valid:
+                return [empty() for _ in waveforms]
+            if speaker == "client":
+                model, scaler = self.client_acoustic_model, self.client_acoustic_scaler
+            else:
+                model, scaler = self.agent_acoustic_model, self.agent_acoustic_scaler
+            if model is None or scaler is None:
+                return [empty() for _ in waveforms]
+            scaled = self._scaled_features([waveforms[i] for i in valid], sample_rate, scaler)
+            ok = ~(np.all(scaled == 0, axis=1) | np.any(np.isnan(scaled), axis=1))
+            predictions = model.predict(scaled)
+            probabilities = model.predict_proba(scaled)
+            results = [empty() for _ in waveforms]
+            for j, i in enumerate(valid):
+                if ok[j]:
+                    results[i] = {"prediction": predictions[j], "confidence": float(probabilities[j].max()),
+                                  "probabilities": probabilities[j].tolist()}
+            return results
+        except Exception as e:
+            self.logger.error(f"Batch acoustic sentiment analysis error: {e}")
+            return [empty() for _ in waveforms]
+

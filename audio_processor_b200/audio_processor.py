@@ -12,13 +12,26 @@ bit-identical to the reference.
 from __future__ import annotations
 
 import ctypes as C
+import logging
 from functools import lru_cache
-from typing import Any, Dict, List, Sequence, Tuple
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
 from . import _native, runtime
 from .feature_extractor import FbankFeatureExtractor, FbankProcessor
+
+
+_CLEAN = str.maketrans("", "", ",?.!-;:\"%'\u00bb\u00ab\u061f()\u060c")
+
+
+def remove_special_characters(text) -> str:
+    """Lower-cases and drops punctuation (Latin and Arabic) like the reference's helper of the same name
+    (utils/utils.py:74-79); ``None`` -> ""."""
+    return "" if text is None else text.lower().translate(_CLEAN)
+
+
+_EMPTY = {"transcription_chunk": "", "agent_transcription": "", "client_transcription": ""}
 
 
 def chunk_table(total_samples: int, chunk_samples: int, step_samples: int) -> List[Tuple[int, int]]:
@@ -54,17 +67,25 @@ class AudioProcessor:
     (``chunk_duration_sec``, ``overlap_sec``, ``target_sample_rate``, ``batch_size`` /
     ``chunk_batch_size``, ``enable_length_bucketing``, ``gpu_index``)."""
 
-    def __init__(self, config: dict, db_manager=None, processor=None):
+    def __init__(self, config: dict, db_manager=None, processor=None, model=None, frontend=None):
         self.config = config
         gpu_index = int(config.get("gpu_index", 0))
         self.device = torch.device(f"cuda:{gpu_index}")
-        self.frontend = runtime.get_frontend(self.device)
+        self._frontend = frontend
         self.db_manager = db_manager
         self.chunk_duration_sec = config["chunk_duration_sec"]
         self.overlap_sec = config.get("overlap_sec", 1)
         self.target_sample_rate = config.get("target_sample_rate", 16000)
         self.processor = processor or FbankProcessor(FbankFeatureExtractor(device=self.device))
-        self.model = None
+        self.model = model                     # callable(input_features=...) -> object with .logits (Wav2Vec2BertForCTC)
+        self.text_cleaner = remove_special_characters
+        self.logger = logging.getLogger(__name__)
+
+    @property
+    def frontend(self) -> "runtime.Frontend":
+        if self._frontend is None:
+            self._frontend = runtime.get_frontend(self.device)
+        return self._frontend
 
     # -------------------------------------------------------------- reference :72-93
     def load_audio(self, audio_path):
@@ -168,3 +189,114 @@ class AudioProcessor:
             per_stream[key] = self.frontend.fbank([c[field].squeeze(0) for c in flat], padding_value=fx.padding_value,
                                                   precision=fx.precision, group_size=gs)
         return [(b, {k: per_stream[k][i] for k in per_stream}) for i, b in enumerate(batches)]
+
+    # -------------------------------------------------------------- reference :162-212
+    def transcribe_batch(self, chunks: List[Dict]) -> List[Dict]:
+        """Length-bucketed batches of ``batch_size`` chunks through ``_process_single_batch``, with the
+        reference's error contract: an exception whose text contains "out of memory" halves the batch size
+        and retries the same slice; any other marks the slice's chunks with empty transcriptions + ``error``.
+
+        Batch assembly stays on the device: the features of the slices ahead are produced by ONE fbank launch
+        per stream (``group_size = batch_size``: every slice padded to its own longest chunk, exactly as one
+        ``processor(...)`` call per slice would) and handed to the model as views -- no numpy hop."""
+        if not chunks:
+            return []
+        batch_size = int(self.config["batch_size"])
+        results: List[Dict] = []
+        if bool(self.config.get("enable_length_bucketing", True)):
+            try:
+                chunks = sorted(chunks, key=lambda c: int(c.get("stereo_waveform", c.get("agent_waveform")).shape[1]))
+            except Exception:
+                pass
+        ahead_n = max(1, int(self.config.get("featurise_ahead_batches", 64)))
+        ahead = None                  # (first chunk, batch size, [features per slice])
+        i = 0
+        while i < len(chunks):
+            batch_end = min(i + batch_size, len(chunks))
+            batch_chunks = chunks[i:batch_end]
+            try:
+                if ahead is None or ahead[1] != batch_size or i >= ahead[0] + batch_size * len(ahead[2]):
+                    ahead = (i, batch_size, self._featurise_ahead(chunks[i:i + ahead_n * batch_size], batch_size))
+                features = ahead[2][(i - ahead[0]) // batch_size]
+                results.extend(self._process_single_batch(batch_chunks, features))
+                self._cleanup_memory()
+            except Exception as e:
+                self.logger.error(f"Error processing batch {i // batch_size + 1}: {e}")
+                if "out of memory" in str(e).lower() and batch_size > 1:
+                    new_bs = max(1, batch_size // 2)
+                    self.logger.warning(f"CUDA OOM detected. Reducing batch size {batch_size} -> {new_bs} and retrying this slice")
+                    batch_size, ahead = new_bs, None
+                    self._release_cache()
+                    continue                                   # retry the same i with the smaller batch
+                for chunk in batch_chunks:
+                    chunk.update({**_EMPTY, "error": str(e)})
+                results.extend(batch_chunks)
+            i = batch_end
+        return results
+
+    def _featurise_ahead(self, chunks: Sequence[Dict], batch_size: int):
+        """Features of consecutive slices of ``batch_size`` chunks: a list of ``{"stereo"|"agent"|"client": input_features}``
+        per slice, or a list of ``None`` when the processor is not the CUDA one (then each slice calls it itself)."""
+        n_slices = (len(chunks) + batch_size - 1) // batch_size
+        fx = getattr(self.processor, "feature_extractor", None)
+        if not isinstance(fx, FbankFeatureExtractor):
+            return [None] * n_slices
+        per_stream = {}
+        for key, field in (("stereo", "stereo_waveform"), ("agent", "agent_waveform"), ("client", "client_waveform")):
+            per_stream[key] = self.frontend.fbank([c[field].squeeze(0) for c in chunks], padding_value=fx.padding_value,
+                                                  precision=fx.precision, group_size=batch_size)
+        return [{k: per_stream[k][g][0] for k in per_stream} for g in range(n_slices)]
+
+    # -------------------------------------------------------------- reference :214-245
+    def _process_single_batch(self, batch_chunks: List[Dict], features: Optional[Dict[str, torch.Tensor]] = None) -> List[Dict]:
+        agent = [chunk["agent_waveform"].squeeze(0) for chunk in batch_chunks]
+        client = [chunk["client_waveform"].squeeze(0) for chunk in batch_chunks]
+        stereo = [chunk["stereo_waveform"].squeeze(0) for chunk in batch_chunks]
+        if torch.cuda.is_available():
+            with torch.autocast("cuda"):
+                results = self._run_inference(stereo, agent, client, features)
+        else:
+            results = self._run_inference(stereo, agent, client, features)
+        for i, chunk in enumerate(batch_chunks):
+            if i < len(results):
+                chunk.update(results[i])
+            else:
+                chunk.update({**_EMPTY, "error": "Index out of range"})
+        return batch_chunks
+
+    # -------------------------------------------------------------- reference :247-309
+    def _run_inference(self, stereo_arrays, agent_arrays, client_arrays,
+                       features: Optional[Dict[str, torch.Tensor]] = None) -> List[Dict]:
+        """Three ``processor(...)`` calls (skipped when ``features`` were produced ahead), the CTC model on each
+        ``input_features`` -- WITHOUT the attention mask, as the reference (:270-272) --, argmax, ``batch_decode``,
+        ``remove_special_characters``.  Any exception becomes a list of empty results carrying its text."""
+        try:
+            if features is None:
+                features = {}
+                for key, arrays in (("stereo", stereo_arrays), ("agent", agent_arrays), ("client", client_arrays)):
+                    inputs = self.processor(arrays, sampling_rate=16000, return_tensors="pt", padding=True)
+                    feat = inputs["input_features"]
+                    features[key] = feat.to(self.device) if torch.cuda.is_available() else feat
+            with torch.no_grad():
+                logits = {k: self.model(input_features=features[k]).logits for k in ("stereo", "agent", "client")}
+            texts = {k: self.processor.batch_decode(torch.argmax(v, dim=-1)) for k, v in logits.items()}
+            cleaned = {k: [self.text_cleaner(t) for t in v] for k, v in texts.items()}
+            return [{"transcription_chunk": cleaned["stereo"][i],
+                     "agent_transcription": cleaned["agent"][i] if i < len(cleaned["agent"]) else "",
+                     "client_transcription": cleaned["client"][i] if i < len(cleaned["client"]) else "",
+                     "error": ""} for i in range(len(cleaned["stereo"]))]
+        except Exception as e:
+            self.logger.error(f"Inference error: {e}")
+            return [{**_EMPTY, "error": str(e)}] * len(stereo_arrays)
+
+    # -------------------------------------------------------------- reference :311-322
+    def _cleanup_memory(self):
+        """The reference collects garbage and empties the CUDA cache after EVERY batch; ``cudaFree`` is a device
+        synchronisation, so here the caching allocator keeps its blocks unless ``release_cache_every_batch``."""
+        if bool(self.config.get("release_cache_every_batch", False)):
+            self._release_cache()
+
+    @staticmethod
+    def _release_cache():
+        if torch.cuda.is_available():
+            torch.cuda.empty_cache()

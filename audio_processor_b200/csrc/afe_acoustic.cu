@@ -65,7 +65,17 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
 int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
                               int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
                               int32_t* d_status, void* d_workspace, size_t workspace_bytes) {
+  return afe_acoustic_batch_scaled(ctx, stream, h_waves, h_lengths, batch, sample_rate, h_out_index, d_out, d_status,
+                                   nullptr, nullptr, 0, nullptr, d_workspace, workspace_bytes);
+}
+
+int afe_acoustic_batch_scaled(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                              int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
+                              int32_t* d_status, const double* d_mean, const double* d_scale, int n_features,
+                              double* d_scaled, void* d_workspace, size_t workspace_bytes) {
   if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_acoustic_batch: bad arguments");
+  if (d_scaled && (!d_mean || !d_scale || n_features <= 0))
+    return fail(AFE_ERR_INVALID, "afe_acoustic_batch_scaled: scaler mean / scale / n_features missing");
   if (batch == 0) return AFE_OK;
   if (sample_rate != 16000)
     return fail(AFE_ERR_UNSUPPORTED, "afe_acoustic_batch: only sample_rate 16000 (frame 400 / hop 160) is built");
@@ -136,7 +146,7 @@ int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_
     rc = afe_launch(ck, AcousticMfccKernel::kSmemBytes, ctx->num_sms * 8, s);
   }
   if (rc == 0) {
-    AcousticFinalKernel fk{d, tile_rec, mfcc_rec, boundary, d_out, d_status};
+    AcousticFinalKernel fk{d, tile_rec, mfcc_rec, boundary, d_out, d_status, d_mean, d_scale, d_scaled, n_features};
     ProfScope ps(ctx, AFE_K_AC_FINAL, s);
     rc = afe_launch(fk, 0, 1 << 20, s);
   }

@@ -491,10 +491,21 @@ struct AcousticMfccKernel {
 struct AcousticFinalKernel {
   static constexpr int kThreads = 32;
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 1;
+  static constexpr int kPhases = 2;
   AcDesc d; const double* tile_rec; const double* mfcc_rec; const float* boundary;
   float* out;              // [B][38]
   int32_t* status;         // [B]
+  // optional StandardScaler epilogue (analyze_batch_sentiment, sentiment_analysis.py:736-752): float64 rows
+  // (x - mean) / scale of the feature LIST the reference hands to scaler.transform -- tempo finished,
+  // zero features for a failed waveform, padded / truncated to n_features
+  const double* sc_mean; const double* sc_scale; double* scaled; int n_features;
+  // the reference's tempo from the flux energy (:869-875, see acoustic.py:_tempo), in float64 like Python
+  AFE_HD static double tempo(double flux_energy, int64_t num_samples) {
+    const int64_t hop = 160, f2 = 1 + num_samples / hop;
+    const int64_t max_lag = flux_energy > 0.0 ? f2 - 2 : 0;
+    const double period = max_lag > 0 ? (double)(max_lag * hop) / 16000.0 : 0.0;
+    return period > 0.0 ? 60.0 / period : 0.0;
+  }
   AFE_HD static void mean_std(double s, double ss, int n, float& mean, float& sd) {
     const double m = s / (double)n;
     mean = (float)m;
@@ -503,11 +514,24 @@ struct AcousticFinalKernel {
   }
   AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return d.B; }
-  AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
+  AFE_HD void phase(int ph, const Item& it, unsigned char*, int tid) const {
     const long item = it.item;
     const long orow = d.out_index ? (long)ldg(d.out_index + item) : item;
     float* o = out + orow * kAcFeat;
     const int F1 = ldg(d.frames1 + item), F2 = ldg(d.frames2 + item);
+    if (ph == 1) {
+      if (scaled == nullptr) return;
+      const int64_t L = ldg(d.len + item);
+      for (int i = tid; i < n_features; i += kThreads) {
+        double x = 0.0;
+        if (F2 > 0 && i < kAcFeat) {
+          x = (double)o[i];
+          if (i == 11) x = tempo(x, L);
+        }
+        scaled[orow * n_features + i] = (x - ldg(sc_mean + i)) / ldg(sc_scale + i);
+      }
+      return;
+    }
     if (F2 <= 0) {                                   // 'Audio too short'
       if (tid == 0) status[orow] = 1;
       for (int i = tid; i < kAcFeat; i += kThreads) o[i] = 0.f;

@@ -305,10 +305,30 @@ class Frontend:
 
     def acoustic_ptrs(self, ptrs: Sequence[int], lens: Sequence[int], sample_rate: int = 16000,
                       out: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
-                      out_index: Optional[Sequence[int]] = None):
+                      out_index: Optional[Sequence[int]] = None, scaler=None, scaled: Optional[torch.Tensor] = None):
         """With ``out`` / ``status`` / ``out_index`` waveform b is written to row ``out_index[b]``
-        of the caller's (N, 38) / (N,) tensors (afe_acoustic_batch_placed)."""
+        of the caller's (N, 38) / (N,) tensors (afe_acoustic_batch_placed).  ``scaler`` = (mean, scale)
+        float64 device vectors of n_features entries: also returns / fills the (N, n_features) float64
+        matrix ``scaler.transform`` would produce (afe_acoustic_batch_scaled)."""
         B = len(ptrs)
+        if scaler is not None:
+            mean, scale = scaler
+            nf = int(mean.numel())
+            if scaled is None:
+                scaled = torch.empty((B if out is None else out.shape[0], nf), dtype=torch.float64, device=self.device)
+            if out is None:
+                out = torch.empty((B, 38), dtype=torch.float32, device=self.device)
+                status = torch.empty((B,), dtype=torch.int32, device=self.device)
+            if B:
+                lens_c = _native.i64_array(lens)
+                idx_c = (C.c_int32 * B)(*[int(i) for i in out_index]) if out_index is not None else None
+                ws = self._workspace2(int(self.lib.afe_acoustic_workspace_bytes(lens_c, B)))
+                with torch.cuda.device(self.device):
+                    self.lib.check(self.lib.afe_acoustic_batch_scaled(
+                        self.ctx, self._stream(), _native.ptr_array(ptrs), lens_c, B, int(sample_rate), idx_c,
+                        C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()), C.c_void_p(mean.data_ptr()),
+                        C.c_void_p(scale.data_ptr()), nf, C.c_void_p(scaled.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel()))
+            return out, status, scaled
         if out is None:
             out = torch.empty((B, 38), dtype=torch.float32, device=self.device)
             status = torch.empty((B,), dtype=torch.int32, device=self.device)

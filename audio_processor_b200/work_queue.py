@@ -8,12 +8,18 @@ reduces across calls, so there is no collective on the data path.
   and a sum of the audio seconds, through ``torch.distributed`` (NCCL on GPUs, gloo on CPU).
 * ``MultiGpuQueue`` -- in-process alternative: one worker thread per visible GPU pulling
   calls dynamically from a shared queue (no 4-GPU cap, stragglers balance).
+* ``ProcessedMarkers`` -- the ``<stem>.done`` / ``<stem>.failed`` marker files of
+  ``DataProcessor`` (services/pipeline.py:280-315), same names and contents, so a run can be
+  resumed by either implementation.
 """
 from __future__ import annotations
 
+import json
 import queue
 import threading
-from typing import Callable, List, Optional, Sequence, Tuple
+from datetime import datetime
+from pathlib import Path
+from typing import Callable, List, Optional, Sequence, Tuple, Union
 
 
 def shard_indices(n_items: int, rank: int, world_size: int) -> List[int]:
@@ -47,12 +53,33 @@ class MultiGpuQueue:
             raise RuntimeError("MultiGpuQueue needs at least one device")
         self.devices = list(devices)
 
-    def map(self, fn: Callable, items: Sequence, set_device: bool = True) -> List:
+    def map(self, fn: Callable, items: Sequence, set_device: bool = True, markers: "Optional[ProcessedMarkers]" = None,
+            max_retries: int = 0) -> List:
+        """Without ``markers`` the first exception stops that worker and is re-raised after the join.  With
+        ``markers`` (items are file paths) the reference's per-file contract applies: files already marked
+        ``.done`` are skipped (result ``None``), a file is retried ``max_retries`` times, then marked ``.failed``
+        with the error text and the other files carry on; successes are marked ``.done``."""
         q: "queue.Queue[Tuple[int, object]]" = queue.Queue()
         for i, it in enumerate(items):
+            if markers is not None and markers.is_already_processed(it):
+                continue
             q.put((i, it))
         out: List = [None] * len(items)
         errors: List[BaseException] = []
+        if markers is not None:
+            inner = fn
+
+            def fn(dev, it):                        # noqa: F811 -- per-file retry + marker wrapper
+                err: Optional[BaseException] = None
+                for _ in range(max(0, int(max_retries)) + 1):
+                    try:
+                        res = inner(dev, it)
+                        markers.mark_file_processed(it)
+                        return res
+                    except Exception as e:
+                        err = e
+                markers.mark_file_failed(it, str(err))
+                return None
 
         def work(dev: int):
             if set_device:
@@ -77,3 +104,33 @@ class MultiGpuQueue:
         if errors:
             raise errors[0]
         return out
+
+
+class ProcessedMarkers:
+    """Idempotence markers of ``DataProcessor`` (services/pipeline.py:280-315): ``<stem>.done`` holds an ISO
+    timestamp, ``<stem>.failed`` a JSON object ``{"timestamp", "error"}``.  Every method swallows I/O errors
+    like the reference (a marker that cannot be written must not fail the file)."""
+
+    def __init__(self, directory: Union[str, Path]):
+        self.dir = Path(directory)
+        self.dir.mkdir(parents=True, exist_ok=True)
+
+    def is_already_processed(self, file_path: Union[str, Path]) -> bool:
+        try:
+            return (self.dir / f"{Path(file_path).stem}.done").exists()
+        except Exception:
+            return False
+
+    def mark_file_processed(self, file_path: Union[str, Path]) -> None:
+        try:
+            (self.dir / f"{Path(file_path).stem}.done").write_text(datetime.now().isoformat())
+        except Exception:
+            pass
+
+    def mark_file_failed(self, file_path: Union[str, Path], error: str = "") -> None:
+        try:
+            content = {"timestamp": datetime.now().isoformat(), "error": error}
+            (self.dir / f"{Path(file_path).stem}.failed").write_text(json.dumps(content))
+        except Exception:
+            pass
+

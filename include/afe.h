@@ -193,6 +193,18 @@ int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_
                               int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
                               int32_t* d_status, void* d_workspace, size_t workspace_bytes);
 
+/* The same with the StandardScaler step of AcousticSentimentAnalyzer.analyze_batch_sentiment
+ * (services/sentiment_analysis.py:736-752) as an epilogue of the last kernel: besides d_out,
+ * row b of d_scaled (float64, [rows][n_features]) receives (x - d_mean) / d_scale of the feature
+ * LIST the reference builds for scaler.transform -- the 38 values in key order with tempo
+ * finished (float64, as Python computes it), all zeros for a waveform whose extraction failed
+ * (status 1 -> _get_zero_features), padded with zeros / truncated to n_features
+ * (scaler.n_features_in_).  Same float64 operations as numpy's (X - mean_) / scale_. */
+int afe_acoustic_batch_scaled(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                              int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
+                              int32_t* d_status, const double* d_mean, const double* d_scale, int n_features,
+                              double* d_scaled, void* d_workspace, size_t workspace_bytes);
+
 /* ---- per-kernel device timing (CUDA events on the caller's stream) --------------------
  * While enabled every kernel launch of this context is bracketed by cudaEvents.
  * afe_profile_read synchronises those events and returns, per kernel id, the summed device

@@ -129,3 +129,21 @@ def acoustic(waves, sample_rate=16000):
     status = np.full((B,), -1, np.int32)
     lib.check(lib.afe_acoustic_batch(ctx, None, ptrs, lens, B, sample_rate, _p(out), _p(status), _p(ws), ws.size))
     return out, status
+
+
+def acoustic_scaled(waves, mean, scale, sample_rate=16000):
+    """afe_acoustic_batch_scaled: (rows (B, 38) f32, status, scaled (B, n_features) f64)."""
+    lib, ctx = emu()
+    waves = [np.ascontiguousarray(w, np.float32).reshape(-1) for w in waves]
+    B = len(waves)
+    lens = _native.i64_array([w.size for w in waves])
+    ptrs = _native.ptr_array([w.ctypes.data for w in waves])
+    ws = np.zeros(lib.afe_acoustic_workspace_bytes(lens, B), np.uint8)
+    out = np.zeros((B, 38), np.float32)
+    status = np.full((B,), -1, np.int32)
+    mean = np.ascontiguousarray(mean, np.float64); scale = np.ascontiguousarray(scale, np.float64)
+    scaled = np.full((B, mean.size), np.nan, np.float64)
+    lib.check(lib.afe_acoustic_batch_scaled(ctx, None, ptrs, lens, B, sample_rate, None, _p(out), _p(status), _p(mean),
+                                            _p(scale), mean.size, _p(scaled), _p(ws), ws.size))
+    return out, status, scaled
+

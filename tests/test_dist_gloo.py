@@ -49,3 +49,30 @@ def test_multi_gpu_queue_dynamic_pull_without_devices():
     assert out == [x * x for x in range(20)]
     with pytest.raises(ZeroDivisionError):
         q.map(lambda dev, x: 1 // x, [1, 0, 2], set_device=False)
+
+
+def test_processed_markers_and_per_file_retries(tmp_path):
+    """The .done / .failed markers of DataProcessor (services/pipeline.py:280-315): names, contents, resume."""
+    import json
+    from datetime import datetime
+    markers = work_queue.ProcessedMarkers(tmp_path / "markers")
+    files = [tmp_path / f"call_{i}.wav" for i in range(6)]
+    markers.mark_file_processed(files[1])                       # finished by an earlier run
+    attempts = {}
+
+    def fn(dev, path):
+        attempts[path.stem] = attempts.get(path.stem, 0) + 1
+        if path.stem == "call_3":
+            raise RuntimeError("decode failed")
+        if path.stem == "call_4" and attempts[path.stem] < 2:
+            raise IOError("transient")
+        return path.stem.upper()
+    out = work_queue.MultiGpuQueue(devices=[0, 1]).map(fn, files, set_device=False, markers=markers, max_retries=1)
+    assert out == ["CALL_0", None, "CALL_2", None, "CALL_4", "CALL_5"]
+    assert "call_1" not in attempts and attempts["call_3"] == 2 and attempts["call_4"] == 2
+    done = sorted(p.name for p in (tmp_path / "markers").glob("*.done"))
+    assert done == ["call_0.done", "call_1.done", "call_2.done", "call_4.done", "call_5.done"]
+    datetime.fromisoformat((tmp_path / "markers" / "call_0.done").read_text())
+    failed = json.loads((tmp_path / "markers" / "call_3.failed").read_text())
+    assert failed["error"] == "decode failed" and set(failed) == {"timestamp", "error"}
+    assert markers.is_already_processed("anywhere/else/call_5.ogg") and not markers.is_already_processed(files[3])
