@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import functools
 import math
+import os
 import time
 import warnings
 from collections import OrderedDict
@@ -150,11 +151,25 @@ def timed_sample(n_workers: int, calls_per_worker: int = 1, seconds: float = 60.
     jobs = [([9000 + w * calls_per_worker + i for i in range(calls_per_worker)], seconds, sample_rate, 1)
             for w in range(n_workers)]
     ctx = mp.get_context("spawn")
-    with ctx.Pool(n_workers) as pool:
-        pool.map(_worker, [([1], 2.0, sample_rate, 1)] * n_workers)          # warm imports / caches
-        t0 = time.perf_counter()
-        res = pool.map(_worker, jobs)
-        wall = time.perf_counter() - t0
+    # one thread per worker process for EVERY library: torch.set_num_threads does not reach numpy's BLAS
+    # (the mel matmul of transformers' spectrogram), and n_workers x n_cores BLAS threads oversubscribe the
+    # box (measured 6.6x slower).  The spawned children inherit these variables.
+    keys = ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS")
+    saved = {k: os.environ.get(k) for k in keys}
+    for k in keys:
+        os.environ[k] = "1"
+    try:
+        with ctx.Pool(n_workers) as pool:
+            pool.map(_worker, [([1], 2.0, sample_rate, 1)] * n_workers)          # warm imports / caches
+            t0 = time.perf_counter()
+            res = pool.map(_worker, jobs)
+            wall = time.perf_counter() - t0
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
     audio_s = sum(r[0] for r in res)
     desc = (f"{n_workers * calls_per_worker} synthetic {seconds:.0f} s stereo {sample_rate} Hz calls, "
             f"{n_workers} processes x 1 thread, full front end (resample+split+chunk+fbank x3+acoustic x2)")
