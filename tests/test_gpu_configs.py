@@ -159,3 +159,45 @@ def test_cfg2_full_size_properties_and_spot_parity(fe):
         from audio_processor_b200.acoustic import TEMPO_SLOT, _tempo
         vals[TEMPO_SLOT] = _tempo(vals[TEMPO_SLOT], e - s, 16000)
         _acoustic_close(vals, list(ref_a.values()))
+
+
+# ------------------------------------------------------------------ threading contract
+def test_concurrent_threads_share_one_processor(fe):
+    """The reference calls split_audio from 8-32 io_executor threads and process_file_batch from up to 16
+    threads on ONE AudioProcessor (audio_processor.py:46-47, 334; pipeline.py:397).  Eight threads, each on its
+    own CUDA stream, run the whole per-file path concurrently; every result must equal the serial one bit for bit."""
+    import threading
+    import torch
+    from audio_processor_b200 import AudioProcessor, acoustic, synth
+    ap = AudioProcessor({"chunk_duration_sec": 25, "overlap_sec": 1, "target_sample_rate": 16000, "batch_size": 16, "gpu_index": 0})
+    calls = [synth.make_call(40.0 + 7.0 * i, 8000, 500 + i, 2) for i in range(8)]
+
+    def one(call, name):
+        chunks, agent, client = ap.split_audio(call, 8000, name)
+        feats = ap.featurise_batch(chunks)
+        rows = acoustic.extract_acoustic_features_batch([c["agent_waveform"] for c in chunks], 16000, fe.device)
+        return agent.clone(), {k: v.clone() for k, v in feats.items()}, rows
+
+    serial = [one(c, f"s{i}") for i, c in enumerate(calls)]
+    torch.cuda.synchronize()
+    out, errs = [None] * len(calls), []
+
+    def work(i):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream(fe.device)):
+                for _ in range(3):                                    # a few rounds to interleave the threads
+                    out[i] = one(calls[i], f"t{i}")
+                torch.cuda.current_stream().synchronize()
+        except BaseException as e:                                    # noqa: BLE001
+            errs.append(e)
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(calls))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errs, errs
+    torch.cuda.synchronize()
+    for (a0, f0, r0), (a1, f1, r1) in zip(serial, out):
+        assert torch.equal(a0, a1)
+        assert f0.keys() == f1.keys() and all(torch.equal(f0[k], f1[k]) for k in f0)
+        assert [list(d.values()) for d in r0] == [list(d.values()) for d in r1]
