@@ -51,12 +51,14 @@ struct AcSmem {
   static constexpr size_t kPOff = (kKeepOff + sizeof(float) * 704 + 15) / 16 * 16;      // float sP[257*32] power
   static constexpr size_t kMOff = kPOff + sizeof(float) * kBins * kTileFrames;           // float sM[257*32] magnitude
   static constexpr size_t kExOff = (kMOff + sizeof(float) * kBins * kTileFrames + 15) / 16 * 16;
-  // the exchange region after stage 2: sDb[32][129] | double part[4][16][32] | float fx,red [16][32] | pf[8][32] | thr[32]
+  // the exchange region after stage 2: sDb[32][129] | double part[3][16][33] | float fx,red [16][33] | pf[8][32]
+  // (role stride 33: lane = frame writes AND lane = role reads of phase 5 are both conflict-free)
+  static constexpr int kRS = 33, kPS = 16 * kRS;
   static constexpr size_t kDbOff = kExOff;
   static constexpr size_t kPartOff = (kDbOff + sizeof(float) * kTileFrames * kDbStride + 15) / 16 * 16;
-  static constexpr size_t kFxOff = kPartOff + sizeof(double) * 4 * 512;
-  static constexpr size_t kRedOff = kFxOff + sizeof(float) * 512;
-  static constexpr size_t kPfOff = kRedOff + sizeof(float) * 512;
+  static constexpr size_t kFxOff = kPartOff + sizeof(double) * 3 * kPS;
+  static constexpr size_t kRedOff = kFxOff + sizeof(float) * kPS;
+  static constexpr size_t kPfOff = kRedOff + sizeof(float) * kPS;
   static constexpr size_t kThrOff = kPfOff + sizeof(float) * 8 * 32;
   static constexpr size_t kDsumOff = kThrOff + sizeof(float) * 64;                   // double dsum[3][32]: total, sum m k, sum m k^2
   static constexpr size_t kHannOff = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // float hann[16][26] (block_init)
@@ -80,9 +82,10 @@ AFE_HD float mag_sqrt(float x) {
 struct AcousticTileKernel {
   static constexpr int kThreads = 512;
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 8;
+  static constexpr int kPhases = 7;
   static constexpr int kTailPhases = 0;
   static constexpr bool kAsyncStage = true;
+  static constexpr int kRS = AcSmem::kRS, kPS = AcSmem::kPS;
   static constexpr size_t kStageOff = AcSmem::kRawOff;
   static constexpr size_t kStageBytes = AcSmem::kRawBytes;
   static constexpr int kPrefetchThread = kThreads - 32;   // lane 0 of the last warp: the lightest one in phase 1
@@ -165,12 +168,10 @@ struct AcousticTileKernel {
     float* sM = reinterpret_cast<float*>(smem + AcSmem::kMOff);        // magnitude
     cplx<float>* ex = reinterpret_cast<cplx<float>*>(smem + AcSmem::kExOff);
     float* sDb = reinterpret_cast<float*>(smem + AcSmem::kDbOff);
-    double* part = reinterpret_cast<double*>(smem + AcSmem::kPartOff);  // [0] e  [1] sum m k  [2] sum m k^2  [3] exclusive prefix of e
+    double* part = reinterpret_cast<double*>(smem + AcSmem::kPartOff);  // [0] e  [1] sum m k  [2] sum m k^2, each [role * 33 + f]
     float* fxp = reinterpret_cast<float*>(smem + AcSmem::kFxOff);
     float* red = reinterpret_cast<float*>(smem + AcSmem::kRedOff);
     float* pf = reinterpret_cast<float*>(smem + AcSmem::kPfOff);       // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
-    float* thrs = reinterpret_cast<float*>(smem + AcSmem::kThrOff);    // [0] threshold  [1] total (float)
-    double* dsum = reinterpret_cast<double*>(smem + AcSmem::kDsumOff); // [0] total  [1] sum m k  [2] sum m k^2 (per frame)
     float* sq16 = keep + AcSmem::kSq;  float* zc16 = keep + AcSmem::kZc;  float* lastx = keep + AcSmem::kLast;
     const int role = tid >> 5, f = tid & 31;
     const int kb = role * 16, ke = (role == 15) ? kBins : kb + 16;       // contiguous bin range of this role
@@ -226,7 +227,7 @@ struct AcousticTileKernel {
           row[m] = db;
           mx = tmax(mx, db);
         });
-        red[tid] = mx;
+        red[role * kRS + f] = mx;
         // moments over k = kb + j with the LOCAL index j (exact small integers), shifted to k once per thread
         double e = 0.0, c = 0.0, c2 = 0.0;
         float fx = 0.f;
@@ -257,78 +258,95 @@ struct AcousticTileKernel {
           c2 = c2 + kd * (2.0 * c + kd * e);
           c = c + kd * e;
         }
-        part[0 * 512 + tid] = e; part[1 * 512 + tid] = c; part[2 * 512 + tid] = c2; fxp[tid] = fx;
-      } break;
-      case 5: {   // per-frame scalars, one 16-step chain per warp: 0 energy prefix, 1 rms / zcr, 2 max dB, 3 / 4 moments, 5 flux
-        if (role == 0) {
-          double tot = 0.0;
-#pragma unroll 4
-          for (int r = 0; r < kRoles; ++r) {
-            part[3 * 512 + r * 32 + f] = tot;               // exclusive prefix: cum_energy before role r's bins
-            tot += part[0 * 512 + r * 32 + f];
-          }
-          const float total = (float)tot;                  // cum_energy[-1] (float64 accumulate like ATen's cumsum)
-          dsum[f] = tot;
-          thrs[f] = 0.85f * (total + 1e-8f);
-          thrs[32 + f] = total;
-        } else if (role == 1) {
-          float s = 0.f, z = 0.f;
-#pragma unroll 5
-          for (int g = 0; g < 25; ++g) { s += sq16[10 * f + g]; z += zc16[10 * f + g]; }
-          pf[4 * 32 + f] = fast_sqrt(s / 400.f);
-          pf[5 * 32 + f] = (z - lastx[f]) / 400.f;
-        } else if (role == 2) {
-          float mx = -3.0e38f;
-#pragma unroll 4
-          for (int r = 0; r < kRoles; ++r) mx = tmax(mx, red[r * 32 + f]);
-          pf[6 * 32 + f] = mx;
-        } else if (role == 3 || role == 4) {
-          const double* src = part + (role - 2) * 512 + f;  // role 3: sum m k, role 4: sum m k^2
-          double acc = 0.0;
-#pragma unroll 4
-          for (int r = 0; r < kRoles; ++r) acc += src[r * 32];
-          dsum[(role - 2) * 32 + f] = acc;
-        } else if (role == 5) {
-          float fx = 0.f;
-#pragma unroll 4
-          for (int r = 0; r < kRoles; ++r) fx += fxp[r * 32 + f];
-          pf[3 * 32 + f] = fx;
+        {
+          const int idx = role * kRS + f;
+          part[idx] = e; part[kPS + idx] = c; part[2 * kPS + idx] = c2; fxp[idx] = fx;
         }
       } break;
-      case 6: {   // rolloff: only the role whose bin range holds the 85 % crossing scans its bins
-        if (role == 0) {   // centroid and bandwidth from the three moments
-          const double tot = dsum[f], C = dsum[32 + f], C2 = dsum[64 + f];
-          const float energy = thrs[32 + f] + 1e-8f;
-          const float cen = 31.25f * (float)C / energy;
+      case 5: {   // per-frame scalars.  Transposed: warp w owns frames 2w, 2w+1; each 16-lane segment is one frame,
+                  // lane r of it holds role r's partials -> reductions over the roles are 4-step shuffle trees and the
+                  // cumulative-energy prefix a 4-step scan; the 16 lanes then share the 16 bins of the crossing role.
+                  // (Float64 sums of float32 magnitudes: the tree and the sequential order agree except where a
+                  // partial sum falls on a float32 rounding boundary of the threshold compare.)
+        const int lane = tid & 31;
+        const int fa = 2 * (tid >> 5) + (lane >> 4), r = lane & 15;
+        const int idx = r * kRS + fa;
+        float cen, bw, roll, fxs, mxs, s, z;
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+        const double e = part[idx], c = part[kPS + idx], c2 = part[2 * kPS + idx];
+        s = sq16[10 * fa + r]; z = zc16[10 * fa + r];
+        if (r < 9) { s += sq16[10 * fa + 16 + r]; z += zc16[10 * fa + 16 + r]; }
+        s = seg16_sum(s); z = seg16_sum(z);
+        fxs = seg16_sum(fxp[idx]); mxs = seg16_max(red[idx]);
+        const double incl = seg16_scan(e, r);                 // cum_energy after role r's bins
+        double lo = __shfl_up_sync(0xffffffffu, incl, 1, 16); // ... before them
+        if (r == 0) lo = 0.0;
+        const double tot = __shfl_sync(0xffffffffu, incl, 15, 16);
+        const double C = seg16_sum(c), C2 = seg16_sum(c2);
+        const float total = (float)tot;                      // cum_energy[-1] (float64 accumulate like ATen's cumsum)
+        const float thr = 0.85f * (total + 1e-8f);
+        const bool lo_below = (r == 0) || ((float)lo < thr);
+        const bool hi_below = ((float)incl < thr);
+        const unsigned cross = (__ballot_sync(0xffffffffu, lo_below && !hi_below) >> (lane & 16)) & 0xffffu;
+        const int rc = cross ? (__ffs((int)cross) - 1) : 15;  // the role whose bins hold the 85 % crossing
+        const double lo_c = __shfl_sync(0xffffffffu, lo, rc, 16);
+        const float* mp = sM + (16 * rc) * kTileFrames + fa;
+        const double pin = seg16_scan(nonneg_to_double(mp[r * kTileFrames]), r);
+        int below = __popc((__ballot_sync(0xffffffffu, (float)(lo_c + pin) < thr) >> (lane & 16)) & 0xffffu);
+        const double p15 = __shfl_sync(0xffffffffu, pin, 15, 16);
+        if (rc == 15)                                        // role 15 has 17 bins: bin 256
+          below += ((float)(lo_c + (p15 + nonneg_to_double(mp[16 * kTileFrames]))) < thr) ? 1 : 0;
+        roll = cross ? 31.25f * (float)(16 * rc + below) : 0.f;   // no bin reaches the threshold: argmax of all-False is 0
+#else
+        if (r != 0) break;                                   // host emulation: lane 0 of the segment walks the same trees
+        double ea[16], ca[16], c2a[16], pin[16];
+        float sa[16], za[16], fa16[16], mx = -3.0e38f;
+        for (int q = 0; q < 16; ++q) {
+          const int iq = q * kRS + fa;
+          ea[q] = part[iq]; ca[q] = part[kPS + iq]; c2a[q] = part[2 * kPS + iq];
+          sa[q] = sq16[10 * fa + q]; za[q] = zc16[10 * fa + q];
+          if (q < 9) { sa[q] += sq16[10 * fa + 16 + q]; za[q] += zc16[10 * fa + 16 + q]; }
+          fa16[q] = fxp[iq]; mx = tmax(mx, red[iq]);
+        }
+        s = tree16_sum(sa); z = tree16_sum(za); fxs = tree16_sum(fa16); mxs = mx;
+        scan16(ea);
+        const double tot = ea[15];
+        const double C = tree16_sum(ca), C2 = tree16_sum(c2a);
+        const float total = (float)tot;
+        const float thr = 0.85f * (total + 1e-8f);
+        int rc = -1;
+        for (int q = 0; q < 16 && rc < 0; ++q) {
+          const bool lo_below = (q == 0) || ((float)ea[q - 1] < thr);
+          if (lo_below && !((float)ea[q] < thr)) rc = q;
+        }
+        roll = 0.f;
+        if (rc >= 0) {
+          const double lo_c = rc ? ea[rc - 1] : 0.0;
+          const float* mp = sM + (16 * rc) * kTileFrames + fa;
+          for (int q = 0; q < 16; ++q) pin[q] = nonneg_to_double(mp[q * kTileFrames]);
+          scan16(pin);
+          int below = 0;
+          for (int q = 0; q < 16; ++q) below += ((float)(lo_c + pin[q]) < thr) ? 1 : 0;
+          if (rc == 15) below += ((float)(lo_c + (pin[15] + nonneg_to_double(mp[16 * kTileFrames]))) < thr) ? 1 : 0;
+          roll = 31.25f * (float)(16 * rc + below);
+        }
+#endif
+        {   // centroid and bandwidth from the three moments
+          const float energy = total + 1e-8f;
+          cen = fast_div(31.25f * (float)C, energy);
           // sum m (31.25 k - cen)^2 from the three moments, in float64
           const double cd = (double)cen;
           const double num = (31.25 * 31.25) * C2 - 2.0 * 31.25 * cd * C + cd * cd * tot;
-          pf[0 * 32 + f] = cen;
-          pf[1 * 32 + f] = fast_sqrt((float)(num > 0.0 ? num : 0.0) / energy);
+          bw = mag_sqrt(fast_div((float)(num > 0.0 ? num : 0.0), energy));
         }
-        const float thr = thrs[f];
-        const double lo = part[3 * 512 + tid];
-        const double hi = lo + part[0 * 512 + tid];         // == the next role's prefix (same additions)
-        const bool lo_below = (role == 0) || ((float)lo < thr);
-        const bool hi_below = ((float)hi < thr);
-        if (role == 15 && hi_below) {
-          pf[2 * 32 + f] = 0.f;                             // no bin reaches the threshold: argmax of all-False is 0
-        } else if (lo_below && !hi_below) {
-          // cum is monotone, so the number of bins below the threshold is a plain count; the only
-          // dependent chain is the 16 additions (rolled loop: cold code, see phase 4)
-          double acc = lo;
-          int below = 0;
-          const float* mp = sM + kb * kTileFrames + f;
-          const int nb = ke - kb;
-#pragma unroll 1
-          for (int j = 0; j < nb; ++j) {
-            acc += nonneg_to_double(mp[j * kTileFrames]);
-            below += ((float)acc < thr) ? 1 : 0;
-          }
-          pf[2 * 32 + f] = 31.25f * (float)(kb + below);
+        if (r == 0) {
+          pf[0 * 32 + fa] = cen; pf[1 * 32 + fa] = bw; pf[2 * 32 + fa] = roll; pf[3 * 32 + fa] = fxs;
+          pf[4 * 32 + fa] = mag_sqrt(s * (1.f / 400.f));
+          pf[5 * 32 + fa] = (z - lastx[fa]) * (1.f / 400.f);
+          pf[6 * 32 + fa] = mxs;
         }
       } break;
-      case 7: {   // tile record (one warp per statistic, lane = frame, fixed-tree reductions), mel-dB rows
+      case 6: {   // tile record (one warp per statistic, lane = frame, fixed-tree reductions), mel-dB rows
         double* rec = tile_rec + it.item * kTileRec;
         if (role < 8) {
           // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff: (sum, sum sq); 5 flux energy; 6 rms range; 7 max dB

@@ -68,6 +68,14 @@ AFE_HD float fast_sqrt(float x) {
   return std::sqrt(x);
 #endif
 }
+// a / b to ~2 ulp (one reciprocal + one multiply): per-frame scalars whose contract is 1e-4 relative
+AFE_HD float fast_div(float a, float b) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  return __fdividef(a, b);
+#else
+  return a / b;
+#endif
+}
 AFE_HD float fma_f(float a, float b, float c) {
 #if AFE_CUDA && defined(__CUDA_ARCH__)
   return __fmaf_rn(a, b, c);
@@ -161,6 +169,40 @@ __device__ __forceinline__ double warp_tree_max(double v) {
   return v;
 }
 #endif
+// 16-lane segments of a warp (two per warp): inclusive Hillis-Steele scan and xor-butterfly reductions.
+// The array forms below run the same additions in the same order (host emulation twins).
+#if AFE_CUDA
+__device__ __forceinline__ double seg16_scan(double v, int r) {
+#pragma unroll
+  for (int d = 1; d < 16; d <<= 1) { const double t = __shfl_up_sync(0xffffffffu, v, d, 16); if (r >= d) v += t; }
+  return v;
+}
+__device__ __forceinline__ double seg16_sum(double v) {
+#pragma unroll
+  for (int w = 1; w < 16; w <<= 1) v += __shfl_xor_sync(0xffffffffu, v, w, 16);
+  return v;
+}
+__device__ __forceinline__ float seg16_sum(float v) {
+#pragma unroll
+  for (int w = 1; w < 16; w <<= 1) v += __shfl_xor_sync(0xffffffffu, v, w, 16);
+  return v;
+}
+__device__ __forceinline__ float seg16_max(float v) {
+#pragma unroll
+  for (int w = 1; w < 16; w <<= 1) { const float o = __shfl_xor_sync(0xffffffffu, v, w, 16); v = o > v ? o : v; }
+  return v;
+}
+#endif
+template <typename T> AFE_HD void scan16(T (&a)[16]) {
+  for (int d = 1; d < 16; d <<= 1)
+    for (int j = 15; j >= d; --j) a[j] = a[j] + a[j - d];
+}
+template <typename T> AFE_HD T tree16_sum(T (&a)[16]) {
+  for (int w = 1; w < 16; w <<= 1)
+    for (int i = 0; i < 16; i += 2 * w) a[i] = a[i] + a[i + w];
+  return a[0];
+}
+
 AFE_HD double tree32_sum(double (&a)[32]) {
   for (int w = 1; w < 32; w <<= 1)
     for (int i = 0; i < 32; i += 2 * w) a[i] = a[i] + a[i + w];
