@@ -63,7 +63,8 @@ struct AcSmem {
   static constexpr size_t kDsumOff = kThrOff + sizeof(float) * 64;                   // double dsum[3][32]: total, sum m k, sum m k^2
   static constexpr size_t kHannOff = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // float hann[16][26] (block_init)
   static constexpr size_t kTwOff = kHannOff + sizeof(float) * kRoles * kWinRow;               // float tw512[16][16][2]
-  static constexpr size_t kBytes = kTwOff + sizeof(float) * kRoles * 32;
+  static constexpr size_t kBndOff = kTwOff + sizeof(float) * kRoles * 32;                      // float sBnd[2][260] boundary spectra
+  static constexpr size_t kBytes = kBndOff + sizeof(float) * 2 * kBoundary;
   static_assert(kDsumOff % 8 == 0 && kDsumOff + sizeof(double) * 96 <= kHannOff, "ex region too small");
 };
 
@@ -172,6 +173,7 @@ struct AcousticTileKernel {
     float* fxp = reinterpret_cast<float*>(smem + AcSmem::kFxOff);
     float* red = reinterpret_cast<float*>(smem + AcSmem::kRedOff);
     float* pf = reinterpret_cast<float*>(smem + AcSmem::kPfOff);       // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
+    float* sBnd = reinterpret_cast<float*>(smem + AcSmem::kBndOff);
     float* sq16 = keep + AcSmem::kSq;  float* zc16 = keep + AcSmem::kZc;  float* lastx = keep + AcSmem::kLast;
     const int role = tid >> 5, f = tid & 31;
     const int kb = role * 16, ke = (role == 15) ? kBins : kb + 16;       // contiguous bin range of this role
@@ -228,31 +230,32 @@ struct AcousticTileKernel {
           mx = tmax(mx, db);
         });
         red[role * kRS + f] = mx;
-        // moments over k = kb + j with the LOCAL index j (exact small integers), shifted to k once per thread
-        double e = 0.0, c = 0.0, c2 = 0.0;
+        // moments over k = kb + j with the LOCAL index j, as running sums taken from the top bin down:
+        //   a += m_j; b += a; q += b   =>   a = sum m, b = sum (j+1) m_j, q = sum (j+1)(j+2)/2 m_j
+        // three float64 additions per bin, no index arithmetic (float32 magnitudes: the sums are exact to ~1e-16)
+        double a = 0.0, b = 0.0, q = 0.0;
         float fx = 0.f;
+        unsigned top = 0u;                                   // largest bit pattern seen (>= 0 floats order like integers)
         const bool has_next = (f + 1 < it.nvalid);
-        // first / last valid frame: their magnitudes are the tile's boundary spectra
-        float* bd = (f == 0) ? boundary + it.item * 2 * kBoundary
-                             : (f == it.nvalid - 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
-        float* bd2 = (f == 0 && it.nvalid == 1) ? boundary + it.item * 2 * kBoundary + kBoundary : nullptr;
+        // first / last valid frame: their magnitudes are the tile's boundary spectra (staged in shared memory,
+        // written out coalesced by the last phase)
+        float* sb = (f == 0) ? sBnd + kb : (f == it.nvalid - 1) ? sBnd + kBoundary + kb : nullptr;
         // a ROLLED loop: the phase runs once per tile, so its cost on the B200 is the instruction fetch of
         // cold code -- 17 unrolled copies of this body were slower than the loop-carried FP64 chains
         {
           const float* mp = sM + kb * kTileFrames + f;
           const int nb = ke - kb;
-          double jd = 0.0;
 #pragma unroll 2
-          for (int j = 0; j < nb; ++j) {
+          for (int j = nb - 1; j >= 0; --j) {
             const float m = mp[j * kTileFrames];
-            const double md = nonneg_to_double(m);
-            e += md; c += md * jd; c2 += md * (jd * jd);
+            top = tmax(top, float_bits(m));
+            a += nonneg_to_double_biased(m); b += a; q += b;
             if (has_next) fx += tmax(mp[j * kTileFrames + 1] - m, 0.f);
-            if (bd) bd[kb + j] = m;
-            if (bd2) bd2[kb + j] = m;
-            jd += 1.0;
+            if (sb) sb[j] = m;
           }
         }
+        if (top > 0x7f7fffffu) a = b = q = (double)bits_float(0x7fc00000u);   // an infinite / NaN magnitude poisons the frame
+        double e = a, c = b - a, c2 = (q + q) - 3.0 * b + a;   // sum m, sum j m, sum j^2 m
         {   // sum m k = kb e + c ; sum m k^2 = kb^2 e + 2 kb c + c2   (all exact products)
           const double kd = (double)kb;
           c2 = c2 + kd * (2.0 * c + kd * e);
@@ -385,6 +388,11 @@ struct AcousticTileKernel {
         }
         float* dst = meldb + (it.row0 + it.f0) * kAcMel;
         for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
+        // boundary spectra: first valid frame, last valid frame (the same frame when the tile holds only one)
+        for (int i = tid; i < 2 * kBins; i += kThreads) {
+          const int second = i >= kBins, k = i - second * kBins;
+          boundary[(it.item * 2 + second) * kBoundary + k] = sBnd[((second && it.nvalid > 1) ? kBoundary : 0) + k];
+        }
       } break;
     }
   }

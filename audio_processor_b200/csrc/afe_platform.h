@@ -150,6 +150,31 @@ AFE_HD double nonneg_to_double(float x) {
 #endif
 }
 
+// The same in two integer instructions for accumulations that tolerate +0 -> 2^-127 (5.9e-39): no zero, infinity
+// or NaN cases.  The caller tracks the largest bit pattern it converted and poisons its sums if that was not finite.
+AFE_HD double nonneg_to_double_biased(float x) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  const unsigned b = __float_as_uint(x);
+  return __hiloint2double((int)((b >> 3) + 0x38000000u), (int)(b << 29));
+#else
+  return x == 0.f ? 0x1p-127 : (double)x;
+#endif
+}
+AFE_HD float bits_float(unsigned b) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  return __uint_as_float(b);
+#else
+  float x; std::memcpy(&x, &b, 4); return x;
+#endif
+}
+AFE_HD unsigned float_bits(float x) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+  return __float_as_uint(x);
+#else
+  unsigned b; std::memcpy(&b, &x, 4); return b;
+#endif
+}
+
 // sum / min / max over the 32 lanes of a warp as the fixed binary tree ((v0+v1)+(v2+v3))+...; every lane
 // gets the result.  tree32_* are the host-emulation twins over an array of the 32 lane values.
 #if AFE_CUDA && defined(__CUDA_ARCH__)
