@@ -253,6 +253,10 @@ struct has_block_init<K, decltype(std::declval<const K&>().block_init((unsigned 
 
 // the thread that derives the next item and issues its TMA copy while the block works on the current
 // one: K::kPrefetchThread if the kernel names a thread whose warp idles in phase 1, else thread 0
+// optional two-segment staging  bool stage_src2(const Item&, const float* (&src)[2], int (&nfloats)[2], int (&dst_float_off)[2]) const
+// (e.g. the two rows of a stereo tile): both copies complete on the item's one mbarrier
+template <class K, class = void> struct has_stage2 { static constexpr bool value = false; };
+template <class K> struct has_stage2<K, decltype((void)K::kStageSegments)> { static constexpr bool value = true; };
 template <class K, class = void> struct prefetch_thread { static constexpr int value = 0; };
 template <class K> struct prefetch_thread<K, decltype((void)K::kPrefetchThread)> { static constexpr int value = K::kPrefetchThread; };
 
@@ -325,6 +329,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // not a plain copy (edges, unaligned pointers) run phase 0 cooperatively.
 // kTrace (debug, AFE_PHASE_TRACE=1): thread 0 adds the cycles between consecutive barriers to
 // trace[block * 16 + phase] (slot 0 = wait for the staged tile, slot 15 = items processed)
+// sets it.bulk and, when the item's staging is a plain copy, arms the mbarrier and issues the TMA bulk copy / copies
+template <class K>
+__device__ __forceinline__ void afe_issue_stage(const K& k, typename K::Item& it, unsigned char* buf, uint64_t* bar) {
+  if constexpr (has_stage2<K>::value) {
+    const float* src[2]; int nf[2], off[2];
+    it.bulk = k.stage_src2(it, src, nf, off) ? 1 : 0;
+    if (it.bulk) {
+      mbar_expect_tx(bar, (uint32_t)(nf[0] + nf[1]) * 4u);
+      bulk_g2s(buf + (size_t)off[0] * 4u, src[0], (uint32_t)nf[0] * 4u, bar);
+      bulk_g2s(buf + (size_t)off[1] * 4u, src[1], (uint32_t)nf[1] * 4u, bar);
+    }
+  } else {
+    const float* src; int nf;
+    it.bulk = k.stage_src(it, src, nf) ? 1 : 0;
+    if (it.bulk) {
+      mbar_expect_tx(bar, (uint32_t)nf * 4u);
+      bulk_g2s(buf, src, (uint32_t)nf * 4u, bar);
+    }
+  }
+}
+
 template <class K, bool kTrace = false>
 __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(const K k, unsigned long long* trace = nullptr) {
   extern __shared__ __align__(16) unsigned char afe_smem[];
@@ -342,13 +367,8 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
       mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_mbar_init();
       typename K::Item c0 = k.prepare(item);
       c0.buf = 0;
-      const float* src; int nf;
-      c0.bulk = k.stage_src(c0, src, nf) ? 1 : 0;
+      afe_issue_stage(k, c0, afe_smem + K::kStageOff, &bars[0]);
       items[0] = c0;
-      if (c0.bulk) {
-        mbar_expect_tx(&bars[0], (uint32_t)nf * 4u);
-        bulk_g2s(afe_smem + K::kStageOff, src, (uint32_t)nf * 4u, &bars[0]);
-      }
     }
     __syncthreads();
     uint32_t parbits = 0u;                 // bit b = phase parity of staging buffer b's mbarrier
@@ -361,15 +381,10 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
       if (tid == prefetch_thread<K>::value && item + 1 < end) {
         typename K::Item nx = k.next(cur, item + 1);
         nx.buf = buf ^ 1;
-        const float* src; int nf;
-        nx.bulk = k.stage_src(nx, src, nf) ? 1 : 0;
+        // no proxy fence: the buffer's last generic-proxy accesses (phase 1 reads, or the phase 0 copy of an
+        // unaligned tile) were performed before the barriers this thread has since passed
+        afe_issue_stage(k, nx, afe_smem + K::kStageOff + (size_t)(buf ^ 1) * K::kStageBytes, &bars[buf ^ 1]);
         items[buf ^ 1] = nx;
-        if (nx.bulk) {
-          // no proxy fence: the buffer's last generic-proxy accesses (phase 1 reads, or the phase 0 copy of an
-          // unaligned tile) were performed before the barriers this thread has since passed
-          mbar_expect_tx(&bars[buf ^ 1], (uint32_t)nf * 4u);
-          bulk_g2s(afe_smem + K::kStageOff + (size_t)(buf ^ 1) * K::kStageBytes, src, (uint32_t)nf * 4u, &bars[buf ^ 1]);
-        }
       }
       if (cur.bulk) { mbar_wait(&bars[buf], (parbits >> buf) & 1u); parbits ^= 1u << buf; }
       else { k.phase(0, cur, afe_smem, tid); __syncthreads(); }

@@ -98,12 +98,12 @@ int launch_up2x(afe_ctx* ctx, cudaStream_t s, const ResampleTaps& t, const UpCal
     Upsample2xKernel<true> k;
     k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = 2; k.nitems = nitems; k.pcm16 = pcm16;
     for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
-    return afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * 8, s);
+    return afe_launch(k, Upsample2xKernel<true>::kSmemBytes, ctx->num_sms * Upsample2xKernel<true>::kMinBlocks, s);
   }
   Upsample2xKernel<false> k;
   k.calls = d_calls; k.one = one; k.ncalls = ncalls; k.rows = rows; k.nitems = nitems; k.pcm16 = pcm16;
   for (int j = 0; j < 2; ++j) for (int i = 0; i < 15; ++i) k.h[j][i] = t.taps[j * 15 + i];
-  return afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * 8, s);
+  return afe_launch(k, Upsample2xKernel<false>::kSmemBytes, ctx->num_sms * Upsample2xKernel<false>::kMinBlocks, s);
 }
 }  // namespace
 

@@ -31,8 +31,14 @@ template <bool STEREO> struct Upsample2xKernel {
   static constexpr int kPos = 1024;                 // input positions per item
   static constexpr int kTile = kPos + 16;           // staged samples per row: x[n0-8 .. n0+1032)
   static constexpr int kRows = STEREO ? 2 : 1;
-  static constexpr size_t kSmemBytes = sizeof(float) * kTile * kRows;
-  static constexpr bool kAsyncStage = false;
+  static constexpr size_t kStageBytes = sizeof(float) * kTile * kRows;      // one staging buffer: the rows' tiles back to back
+  // stereo launches: a block owns a contiguous run of items and the rows of item i+1 arrive by two TMA bulk copies
+  // while item i is computed (float input; PCM input is converted cooperatively in phase 0)
+  static constexpr bool kAsyncStage = STEREO;
+  static constexpr int kStageSegments = 2;
+  static constexpr int kTailPhases = 0;
+  static constexpr size_t kStageOff = 0;
+  static constexpr size_t kSmemBytes = kStageBytes * (STEREO ? 2 : 1);
 
   const UpCall* calls;    // device array [ncalls] (nullptr: `one`)
   UpCall one;
@@ -43,13 +49,13 @@ template <bool STEREO> struct Upsample2xKernel {
   long nitems;
   float h[2][15];
 
-  struct Item { long item; int buf; int bulk; const float* src; float* dst; float* mix; int64_t L; int64_t n0; };
+  struct Item { long item; int buf; int bulk; int ci; const float* src; float* dst; float* mix; int64_t L; int64_t n0; };
 
   AFE_HD long num_items() const { return nitems; }
 
   AFE_HD Item prepare(long item) const {
     Item it;
-    it.item = item; it.buf = 0; it.bulk = 0;
+    it.item = item; it.buf = 0; it.bulk = 0; it.ci = 0;
     UpCall c;
     if (calls == nullptr) {
       c = one;
@@ -62,6 +68,7 @@ template <bool STEREO> struct Upsample2xKernel {
       c.in = ldg(&calls[lo].in); c.out = const_cast<float*>(ldg(const_cast<const float* const*>(&calls[lo].out)));
       c.mixed = const_cast<float*>(ldg(const_cast<const float* const*>(&calls[lo].mixed)));
       c.L = ldg(&calls[lo].L); c.item0 = ldg(&calls[lo].item0);
+      it.ci = lo;
     }
     const long local = item - (long)c.item0;
     const long ipr = (long)((c.L + kPos - 1) / kPos);
@@ -76,8 +83,32 @@ template <bool STEREO> struct Upsample2xKernel {
     return it;
   }
 
+  // item cur.item + 1 of a stereo launch without a search: the next 1024 positions of the same call, else the
+  // first item of the next call that has samples
+  AFE_HD Item next(const Item& cur, long item) const {
+    Item it = cur;
+    it.item = item;
+    if (cur.n0 + kPos < cur.L) { it.n0 = cur.n0 + kPos; return it; }
+    int ci = cur.ci + 1;
+    while (ci + 1 < ncalls && ldg(&calls[ci].L) <= 0) ++ci;
+    it.ci = ci; it.n0 = 0;
+    it.src = ldg(&calls[ci].in);
+    it.dst = const_cast<float*>(ldg(const_cast<const float* const*>(&calls[ci].out)));
+    it.mix = const_cast<float*>(ldg(const_cast<const float* const*>(&calls[ci].mixed)));
+    it.L = ldg(&calls[ci].L);
+    return it;
+  }
+  // interior tiles of float input: rows x[n0-8 .. n0+1032) are two aligned contiguous copies
+  AFE_HD bool stage_src2(const Item& it, const float* (&src)[2], int (&nf)[2], int (&off)[2]) const {
+    const float* p0 = it.src + (it.n0 - 8);
+    src[0] = p0; src[1] = p0 + it.L;
+    nf[0] = nf[1] = kTile; off[0] = 0; off[1] = kTile;
+    return STEREO && pcm16 == 0 && it.n0 >= 8 && it.n0 - 8 + kTile <= it.L &&
+           ((reinterpret_cast<uintptr_t>(p0) | reinterpret_cast<uintptr_t>(p0 + it.L)) & 15u) == 0;
+  }
+
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
-    float* xs = reinterpret_cast<float*>(smem);
+    float* xs = reinterpret_cast<float*>(smem + (size_t)it.buf * kStageBytes);
     const int64_t n0 = it.n0, L = it.L;
     if (ph == 0 && pcm16 == 2) {
       // frames as they lie in a wav file: sample (g, r) at src[g * rows + r]; it.src already points at row0

@@ -186,6 +186,7 @@ def run_afe(a):
         r = cf.process_calls(dev_calls, 8000, acoustic_to_host=False)
     n_chunks = len(r.chunks)
     frames_per_stream = sum(1 + (e - s - 400) // 160 for _, _, s, e in r.chunks if e - s >= 400)
+    stft_frames = sum(1 + (e - s) // 160 for _, _, s, e in r.chunks if e - s >= 400)      # centred STFT of the acoustic path
     del r
     torch.cuda.synchronize(dev)
 
@@ -262,6 +263,18 @@ def run_afe(a):
         achieved = frames_per_launch * FBANK_BYTES_PER_FRAME / (fb_ms / max(fb_n, 1) * 1e-3) / 1e9 if fb_ms > 0 else None
         traffic_pf = ncu_traffic()
         kernel_ms = {k: round(v[0] / a.steps, 4) for k, v in prof.items() if v[1]}
+        # the other kernels against the same HBM roof (algorithmic bytes of SURVEY.md 8d per step and GPU):
+        # resample 8 kHz stereo 256 000 B per call-second; acoustic tile 640 B per 10 ms frame of each speaker;
+        # MFCC pass: the 128 mel-dB floats of every frame, written by the tile kernel and read back once
+        step_bytes = {"resample": 256000.0 * a.calls * a.call_seconds,
+                      "acoustic_tile": 2.0 * stft_frames * (640.0 + 512.0),
+                      "acoustic_mfcc": 2.0 * stft_frames * 512.0}
+        other = {}
+        for k, nbytes in step_bytes.items():
+            if k in prof and prof[k][0] > 0:
+                gbps = nbytes / (prof[k][0] / a.steps * 1e-3) / 1e9
+                other[k] = {"achieved": round(gbps, 1), "frac": round(gbps / peak, 4), "unit": "GB/s",
+                            "algorithmic_bytes_per_step": nbytes}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -287,6 +300,7 @@ def run_afe(a):
                          "algorithmic_bytes_per_launch": frames_per_launch * FBANK_BYTES_PER_FRAME,
                          "launches_timed": fb_n, "avg_launch_ms": fb_ms / max(fb_n, 1),
                          "note": "fp64-issue-bound, not HBM-bound: see DESIGN.md section 5"},
+            "roofline_other_kernels": other,
         }
         if world == 1 and not a.no_cpu_baseline:
             from oracle import libref
