@@ -201,3 +201,45 @@ def test_concurrent_threads_share_one_processor(fe):
         assert torch.equal(a0, a1)
         assert f0.keys() == f1.keys() and all(torch.equal(f0[k], f1[k]) for k in f0)
         assert [list(d.values()) for d in r0] == [list(d.values()) for d in r1]
+
+
+# ------------------------------------------------------------------ cfg4: calls sharded by file over the visible GPUs
+def test_cfg4_queue_shards_files_over_all_visible_gpus(fe, tmp_path):
+    """cfg4 at test size: wav files pulled from the host queue by one worker per visible GPU
+    (multi_gpu_manager.py:67-139 is the reference's static deal; here any GPU count, dynamic pull).
+    Whatever device a file lands on, its outputs equal the single-device ones bit for bit; `.done`
+    markers make a second run a no-op.  With one visible GPU the queue has one worker."""
+    import torch
+    from audio_processor_b200 import CallFrontend, synth, wav, work_queue
+    n_dev = torch.cuda.device_count()
+    files = []
+    for i in range(3 * max(n_dev, 2)):
+        call = synth.make_call(26.0 + 3.0 * (i % 4), 8000, 900 + i, 2)
+        p = tmp_path / f"call_{i:02d}.wav"
+        p.write_bytes(synth.wav_image(call, 8000).numpy().tobytes())
+        files.append(p)
+    fronts = {d: CallFrontend(torch.device("cuda", d)) for d in range(n_dev)}
+    used = []
+
+    def one(dev, path):
+        pcm, sr = wav.load_pcm16(wav.read_pinned(path))
+        r = fronts[dev].process_calls([pcm], sr)
+        torch.cuda.synchronize(dev)
+        used.append(dev)
+        feats = {k: [(f.cpu(), m.cpu()) for f, m in v] for k, v in r.features.items()}
+        return r.chunks, feats, r.acoustic_rows.clone(), r.waveforms[0][0].cpu()
+
+    serial = [one(0, p) for p in files]
+    used.clear()
+    markers = work_queue.ProcessedMarkers(tmp_path / "markers")
+    out = work_queue.MultiGpuQueue().map(one, files, markers=markers, max_retries=1)
+    assert sorted(set(used)) == list(range(n_dev)) or len(files) < n_dev
+    for (c0, f0, a0, w0), got in zip(serial, out):
+        assert got is not None
+        c1, f1, a1, w1 = got
+        assert c0 == c1 and torch.equal(w0, w1) and torch.equal(a0, a1)
+        assert f0.keys() == f1.keys()
+        for k in f0:
+            assert all(torch.equal(x0, x1) and torch.equal(m0, m1) for (x0, m0), (x1, m1) in zip(f0[k], f1[k]))
+    assert all(markers.is_already_processed(p) for p in files)
+    assert work_queue.MultiGpuQueue().map(one, files, markers=markers) == [None] * len(files)   # resumed run: nothing left
