@@ -130,7 +130,7 @@ int afe_acoustic_batch_scaled(afe_ctx* ctx, void* stream, const float* const* h_
   float* meldb = reinterpret_cast<float*>(ws + l.off_meldb);
 
   AcousticTileKernel tk;
-  tk.d = d; tk.hann = ctx->d_hann32; tk.tw512 = ctx->d_tw32;
+  tk.d = d; tk.hann = ctx->d_hann32; tk.tw512 = ctx->d_tw32; tk.mel_w = ctx->htk_slots.w; tk.mel_start = ctx->htk_slots.start;
   tk.meldb = meldb; tk.tile_rec = tile_rec; tk.boundary = boundary;
   int rc;
   { ProfScope ps(ctx, AFE_K_AC_TILE, s); rc = afe_launch(tk, AcSmem::kBytes, ctx->num_sms, s); }

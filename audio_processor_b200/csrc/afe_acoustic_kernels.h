@@ -64,7 +64,9 @@ struct AcSmem {
   static constexpr size_t kHannOff = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // float hann[16][26] (block_init)
   static constexpr size_t kTwOff = kHannOff + sizeof(float) * kRoles * kWinRow;               // float tw512[16][16][2]
   static constexpr size_t kBndOff = kTwOff + sizeof(float) * kRoles * 32;                      // float sBnd[2][260] boundary spectra
-  static constexpr size_t kBytes = kBndOff + sizeof(float) * 2 * kBoundary;
+  static constexpr size_t kMelWOff = (kBndOff + sizeof(float) * 2 * kBoundary + 15) / 16 * 16;   // float melw[16][40] slot-form HTK bank (block_init)
+  static constexpr size_t kMelSOff = kMelWOff + sizeof(float) * kRoles * kMelSlotRow;            // int32 mels[16][8]
+  static constexpr size_t kBytes = kMelSOff + sizeof(int32_t) * kRoles * kMelSlotStarts;
   static_assert(kDsumOff % 8 == 0 && kDsumOff + sizeof(double) * 96 <= kHannOff, "ex region too small");
 };
 
@@ -96,6 +98,8 @@ struct AcousticTileKernel {
   AcDesc d;
   const float* hann;        // [16][26] role-major: periodic Hann[16 n1 + role] / 2
   const float* tw512;       // [16][16][2]
+  const float* mel_w;       // [16][40] slot-form HTK bank (afe_mel_slots.h)
+  const int32_t* mel_start; // [16][8]
   float* meldb;             // [rows][128]
   double* tile_rec;         // [ntiles][16]
   float* boundary;          // [ntiles][2][260]  first / last valid frame magnitudes
@@ -107,6 +111,10 @@ struct AcousticTileKernel {
     float* t = reinterpret_cast<float*>(smem + AcSmem::kTwOff);
     for (int i = tid; i < kRoles * kWinRow; i += kThreads) w[i] = ldg(hann + i);
     for (int i = tid; i < kRoles * 32; i += kThreads) t[i] = ldg(tw512 + i);
+    float* mw = reinterpret_cast<float*>(smem + AcSmem::kMelWOff);
+    int32_t* ms = reinterpret_cast<int32_t*>(smem + AcSmem::kMelSOff);
+    for (int i = tid; i < kRoles * kMelSlotRow; i += kThreads) mw[i] = ldg(mel_w + i);
+    for (int i = tid; i < kRoles * kMelSlotStarts; i += kThreads) ms[i] = ldg(mel_start + i);
   }
 
   AFE_HD Item prepare(long item) const {
@@ -189,26 +197,48 @@ struct AcousticTileKernel {
         }
       } break;
       case 1: {   // padded copy for the STFT + 16-sample partials of the unfold frames
-        {         // element i = tid + 512 j sits at i + (i >> 5) = tid + role + 528 j
-          float* dp = dbuf + tid + role;
-          const float* rp = raw + tid;
+        {         // 128-bit loads; the four words of chunk v land at 4 v + (v >> 3) + e (conflict-free both ways)
+          const float4* r4 = reinterpret_cast<const float4*>(raw);
 #pragma unroll
-          for (int j = 0; j < kTileSamples / kThreads; ++j) dp[(kThreads + 16) * j] = rp[kThreads * j];
-          if (tid < kTileSamples % kThreads) dp[(kThreads + 16) * (kTileSamples / kThreads)] = rp[kThreads * (kTileSamples / kThreads)];
+          for (int j = 0; j < (kTileSamples / 4 + kThreads - 1) / kThreads; ++j) {
+            const int v = tid + kThreads * j;
+            if (v < kTileSamples / 4) {
+              const float4 x = r4[v];
+              float* dp = dbuf + 4 * v + (v >> 3);
+              dp[0] = x.x; dp[1] = x.y; dp[2] = x.z; dp[3] = x.w;
+            }
+          }
         }
         if (tid < kGroups16) {
-          float s = 0.f, z = 0.f;
-#pragma unroll 4
-          for (int j = 0; j < 16; ++j) {
-            const int i = 200 + tid * 16 + ((j + tid) & 15);           // rotated: 2-way bank conflicts
-            const float a = raw[i], c = raw[i + 1];
-            s = fma_f(a, a, s);
-            z += crossing(a, c) ? 1.f : 0.f;
+          // group t = unfold samples [16 t, 16 t + 16) = raw[200 + 16 t ...]: sum of squares and the number of sign
+          // changes over the pairs (i - 1, i) ENDING in the group.  Signs as exact small floats: s = [x > 0] - [x < 0],
+          // n = s^2 = [x != 0]; a pair crosses iff s_a s_c = -1, so crossings = (sum n_a n_c - sum s_a s_c) / 2 -- two
+          // FMAs per pair, no branches, zeros never count (sentiment_analysis.py:830-832).
+          const int t = tid;
+          const float4* g4 = reinterpret_cast<const float4*>(raw + 200 + 16 * t);
+          const float xprev = raw[200 + 16 * t - 1];
+          float sb = ((xprev > 0.f) ? 1.f : 0.f) - ((xprev < 0.f) ? 1.f : 0.f), nb = sb * sb;
+          float sq = 0.f, zn = 0.f, zs = 0.f;
+#pragma unroll 1
+          for (int q = 0; q < 4; ++q) {          // rolled: the phase runs once per tile, compact code beats ILP here
+            const float4 v = g4[q];
+            const float s0 = ((v.x > 0.f) ? 1.f : 0.f) - ((v.x < 0.f) ? 1.f : 0.f);
+            const float s1 = ((v.y > 0.f) ? 1.f : 0.f) - ((v.y < 0.f) ? 1.f : 0.f);
+            const float s2 = ((v.z > 0.f) ? 1.f : 0.f) - ((v.z < 0.f) ? 1.f : 0.f);
+            const float s3 = ((v.w > 0.f) ? 1.f : 0.f) - ((v.w < 0.f) ? 1.f : 0.f);
+            const float n0 = s0 * s0, n1 = s1 * s1, n2 = s2 * s2, n3 = s3 * s3;
+            zn = fma_f(nb, n0, zn); zs = fma_f(sb, s0, zs);
+            zn = fma_f(n0, n1, zn); zs = fma_f(s0, s1, zs);
+            zn = fma_f(n1, n2, zn); zs = fma_f(s1, s2, zs);
+            zn = fma_f(n2, n3, zn); zs = fma_f(s2, s3, zs);
+            sq = fma_f(v.x, v.x, sq); sq = fma_f(v.y, v.y, sq); sq = fma_f(v.z, v.z, sq); sq = fma_f(v.w, v.w, sq);
+            sb = s3; nb = n3;
           }
-          sq16[tid] = s; zc16[tid] = z;
+          sq16[t] = sq;
+          zc16[t] = 0.5f * (zn - zs);
         }
-        if (tid < kTileFrames)     // the pair (399, 400) of unfold frame tid is NOT part of the frame
-          lastx[tid] = crossing(raw[200 + kHop * tid + 399], raw[200 + kHop * tid + 400]) ? 1.f : 0.f;
+        if (tid < kTileFrames)     // the pair (-1, 0) of unfold frame tid is counted by its first group but is NOT part of the frame
+          lastx[tid] = crossing(raw[200 + kHop * tid - 1], raw[200 + kHop * tid]) ? 1.f : 0.f;
       } break;
       case 2: {   // Hann window + stage 1 of the real FFT
         float r[25];
@@ -221,10 +251,11 @@ struct AcousticTileKernel {
       case 3:     // stage 2: power (mel bank) and magnitude (spectral features)
         rfft512_stage2<float, true>(role, f, ex, sP, sM);
         break;
-      case 4: {   // 128 HTK mel filters -> dB rows; moments / flux of this role's contiguous bins
+      case 4: {   // 128 HTK mel filters (slot form) -> dB rows; moments / flux of this role's contiguous bins
         float mx = -3.0e38f;
         float* row = sDb + f * kDbStride;
-        mel_filters_htk<kTileFrames>(role, f, sP, [row, &mx](int m, float acc) {
+        mel_slots_htk<kTileFrames>(role, f, sP, reinterpret_cast<const float*>(smem + AcSmem::kMelWOff),
+                                   reinterpret_cast<const int32_t*>(smem + AcSmem::kMelSOff), [row, &mx](int m, float acc) {
           const float db = 10.f * fast_log10(tmax(acc, 1e-10f));
           row[m] = db;
           mx = tmax(mx, db);

@@ -52,6 +52,8 @@ struct afe_ctx {
   MelDev kaldi_mel_dev{}, htk_mel_dev{};
   struct MelIvPtr { const afe::MelIvOp* ops; const int32_t* role_op; };
   MelIvPtr kaldi_iv{}, htk_iv{};                                 // table-driven banks (afe_mel_loop.h)
+  struct MelSlotPtr { const float* w; const int32_t* start; };   // slot-form banks (afe_mel_slots.h): [16][40], [16][8]
+  MelSlotPtr kaldi_slots{}, htk_slots{};
   std::mutex mu;
   std::map<std::pair<int, int>, afe::DeviceTaps> taps;          // (orig, new) -> bank
   std::vector<afe::StagingBlock> staging;

@@ -51,6 +51,7 @@ int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, dou
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
   k.mask = mask; k.padding_value = padding_value;
   k.log_floor = ctx->log_floor;
+  k.mel_w = ctx->kaldi_slots.w; k.mel_start = ctx->kaldi_slots.start;
   ProfScope ps(ctx, AFE_K_FBANK, s);
   return afe_launch(k, FbankKernel<T>::S::kBytes, ctx->num_sms * FbankKernel<T>::kMinBlocks, s);
 }

@@ -13,6 +13,7 @@
 // in float.
 #pragma once
 #include "afe_mel_gen.h"
+#include "afe_mel_slots.h"
 #include "afe_rfft512.h"
 #include "afe_tables.h"
 
@@ -112,7 +113,10 @@ template <typename T, int TF> struct FbankSmem {
   static constexpr size_t kExBytesT = sizeof(cplx<T>) * 16 * 16 * TF;
   static constexpr size_t kWinOff = kExOff + kExBytesT;                             // T window[16][26] (block_init)
   static constexpr size_t kTwOff = kWinOff + sizeof(T) * kRoles * kWinRow;          // T tw512[16][16][2]
-  static constexpr size_t kBytes = kTwOff + sizeof(T) * kRoles * 32;
+  static constexpr size_t kMelWOff = kTwOff + sizeof(T) * kRoles * 32;              // float melw[16][40]  slot-form mel bank (block_init)
+  static constexpr size_t kMelSOff = kMelWOff + sizeof(float) * kRoles * kMelSlotRow;   // int32 mels[16][8]
+  static constexpr size_t kBytes = kMelSOff + sizeof(int32_t) * kRoles * kMelSlotStarts;
+  static_assert(kMelWOff % 16 == 0, "mel weight rows are read as 128-bit words");
   static_assert(kSamples % 80 == 0 && kG80 == 2 * TF + 3, "tile samples must split into groups of 16 and 80");
 };
 
@@ -141,6 +145,8 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
   double* partials;        // [ntiles][80][2]  (sum, sum of squares) per mel bin
   const T* window;         // [16][26] role-major: povey[16 n1 + role] * 32768 / 2   (copied to shared memory
   const T* tw512;          // [16][16][2]                                            once per block: block_init)
+  const float* mel_w;      // [16][40] slot-form Kaldi bank (afe_mel_slots.h), copied to shared memory by block_init
+  const int32_t* mel_start;   // [16][8]
   float log_floor;         // float32(log(float64(mel_floor)))
   int32_t* mask;           // [rows/2]   (fused normalisation only)
   float padding_value;
@@ -155,6 +161,10 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
     T* t = reinterpret_cast<T*>(smem + S::kTwOff);
     for (int i = tid; i < kRoles * kWinRow; i += kThreads) w[i] = ldg(window + i);
     for (int i = tid; i < kRoles * 32; i += kThreads) t[i] = ldg(tw512 + i);
+    float* mw = reinterpret_cast<float*>(smem + S::kMelWOff);
+    int32_t* ms = reinterpret_cast<int32_t*>(smem + S::kMelSOff);
+    for (int i = tid; i < kRoles * kMelSlotRow; i += kThreads) mw[i] = ldg(mel_w + i);
+    for (int i = tid; i < kRoles * kMelSlotStarts; i += kThreads) ms[i] = ldg(mel_start + i);
   }
 
   AFE_HD void fill(Item& it, int b, int f0) const {
@@ -312,10 +322,11 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
       case 3:
         rfft512_stage2<T, false, TF>(role, f, ex, sP);
         break;
-      case 4: {   // triangular mel bank (generated straight-line code) + floor + log
+      case 4: {   // triangular mel bank (slot form: one code path for all roles) + floor + log
         float* row = sOut + f * kOutStride;
         const float lf = log_floor;
-        mel_filters_kaldi<TF>(role, f, sP, [row, lf](int m, float acc) {
+        mel_slots_kaldi<TF>(role, f, sP, reinterpret_cast<const float*>(smem + S::kMelWOff),
+                            reinterpret_cast<const int32_t*>(smem + S::kMelSOff), [row, lf](int m, float acc) {
           row[m] = (acc <= kMelFloor) ? lf : fast_log(acc);
         });
       } break;

@@ -244,6 +244,9 @@ int afe_create(int device, afe_ctx** out) {
          (c->kaldi_mel_dev.iv_start = c->upload(mel.iv_start)) && (c->kaldi_mel_dev.iv_count = c->upload(mel.iv_count)) &&
          (c->kaldi_mel_dev.role_iv = c->upload(mel.role_iv));
     { const MelIvOps mo = make_mel_iv_ops(mel); ok = ok && (c->kaldi_iv.ops = c->upload(mo.ops)) && (c->kaldi_iv.role_op = c->upload(mo.role_op)); }
+    { const MelSlots ms = make_mel_slots(mel, kKaldiSlotLen, 5);
+      if (!ms.ok) note_error("afe_create", "Kaldi mel bank does not fit the kernels' slot lengths");
+      ok = ok && ms.ok && (c->kaldi_slots.w = c->upload(ms.w)) && (c->kaldi_slots.start = c->upload(ms.start)); }
     std::vector<double> hn = make_hann_periodic();
     std::vector<float> hn32(16 * 26, 0.f);
     for (size_t i = 0; i < hn.size(); ++i) hn32[(i % 16) * 26 + i / 16] = (float)(hn[i] * 0.5);
@@ -255,6 +258,9 @@ int afe_create(int device, afe_ctx** out) {
          (c->htk_mel_dev.iv_start = c->upload(htk.iv_start)) && (c->htk_mel_dev.iv_count = c->upload(htk.iv_count)) &&
          (c->htk_mel_dev.role_iv = c->upload(htk.role_iv));
     { const MelIvOps mo = make_mel_iv_ops(htk); ok = ok && (c->htk_iv.ops = c->upload(mo.ops)) && (c->htk_iv.role_op = c->upload(mo.role_op)); }
+    { const MelSlots ms = make_mel_slots(htk, kHtkSlotLen, 8);
+      if (!ms.ok) note_error("afe_create", "HTK mel bank does not fit the kernels' slot lengths");
+      ok = ok && ms.ok && (c->htk_slots.w = c->upload(ms.w)) && (c->htk_slots.start = c->upload(ms.start)); }
     c->h_dct = make_dct_matrix();
     ok = ok && (c->d_dct = c->upload(c->h_dct));
     c->log_floor = (float)std::log((double)kMelFloor);

@@ -200,4 +200,28 @@ MelIvOps make_mel_iv_ops(const SparseBank& b) {
   return out;
 }
 
+MelSlots make_mel_slots(const SparseBank& b, const int* slot_len, int nslots) {
+  MelSlots out;
+  out.w.assign((size_t)16 * kMelSlotRow, 0.f);
+  out.start.assign((size_t)16 * kMelSlotStarts, 0);
+  out.ok = (b.filters == 16 * nslots) && nslots <= kMelSlotStarts;
+  if (!out.ok) return out;
+  for (int r = 0; r < 16; ++r) {
+    int off = 0;
+    for (int s = 0; s < nslots; ++s) {
+      const int L = slot_len[s];
+      const int m = 16 * s + ((s & 1) ? 15 - r : r);
+      const int count = b.count[(size_t)m];
+      if (count > L || off + L > kMelSlotRow) { out.ok = false; return out; }
+      int first = b.start[(size_t)m];
+      if (first + L > kBins) first = kBins - L;               // keep the padded reads inside the spectrum
+      const int shift = b.start[(size_t)m] - first;
+      for (int i = 0; i < count; ++i) out.w[(size_t)r * kMelSlotRow + off + shift + i] = b.w[(size_t)b.offset[(size_t)m] + i];
+      out.start[(size_t)r * kMelSlotStarts + s] = first;
+      off += L;
+    }
+  }
+  return out;
+}
+
 }  // namespace afe

@@ -57,6 +57,21 @@ struct MelIvOps {
 };
 MelIvOps make_mel_iv_ops(const SparseBank& bank);
 
+// Slot form for the device (afe_mel_slots.h): filter (role r, slot s) = 16 s + (s even ? r : 15 - r); slot s is
+// padded to slot_len[s] bins (zero weights; the first bin moves down where the padding would pass bin 256).
+// w[16][kMelSlotRow] rows of weights, slots back to back; start[16][kMelSlotStarts] first bin of every slot.
+// ok = false when a filter is wider than its slot (the kernels' slot lengths are compile-time constants).
+constexpr int kMelSlotRow = 40;          // floats per role (both banks: 4+4+6+10+16 = 40, 2+2+2+3+4+6+8+11 = 38)
+constexpr int kMelSlotStarts = 8;
+constexpr int kKaldiSlotLen[5] = {4, 4, 6, 10, 16};
+constexpr int kHtkSlotLen[8] = {2, 2, 2, 3, 4, 6, 8, 11};
+struct MelSlots {
+  std::vector<float> w;
+  std::vector<int32_t> start;
+  bool ok = false;
+};
+MelSlots make_mel_slots(const SparseBank& bank, const int* slot_len, int nslots);
+
 std::vector<double> make_povey_window();           // 400, symmetric hann^0.85
 std::vector<double> make_hann_periodic();          // 400
 std::vector<double> make_twiddle512();             // [16][16][2]: e^{-2 pi i n2 k1 / 512}
