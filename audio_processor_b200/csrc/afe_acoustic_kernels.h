@@ -181,7 +181,6 @@ struct AcousticTileKernel {
     float* fxp = reinterpret_cast<float*>(smem + AcSmem::kFxOff);
     float* red = reinterpret_cast<float*>(smem + AcSmem::kRedOff);
     float* pf = reinterpret_cast<float*>(smem + AcSmem::kPfOff);       // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
-    float* sBnd = reinterpret_cast<float*>(smem + AcSmem::kBndOff);
     float* sq16 = keep + AcSmem::kSq;  float* zc16 = keep + AcSmem::kZc;  float* lastx = keep + AcSmem::kLast;
     const int role = tid >> 5, f = tid & 31;
     const int kb = role * 16, ke = (role == 15) ? kBins : kb + 16;       // contiguous bin range of this role
@@ -268,21 +267,17 @@ struct AcousticTileKernel {
         float fx = 0.f;
         unsigned top = 0u;                                   // largest bit pattern seen (>= 0 floats order like integers)
         const bool has_next = (f + 1 < it.nvalid);
-        // first / last valid frame: their magnitudes are the tile's boundary spectra (staged in shared memory,
-        // written out coalesced by the last phase)
-        float* sb = (f == 0) ? sBnd + kb : (f == it.nvalid - 1) ? sBnd + kBoundary + kb : nullptr;
         // a ROLLED loop: the phase runs once per tile, so its cost on the B200 is the instruction fetch of
         // cold code -- 17 unrolled copies of this body were slower than the loop-carried FP64 chains
         {
           const float* mp = sM + kb * kTileFrames + f;
           const int nb = ke - kb;
-#pragma unroll 2
+#pragma unroll 4
           for (int j = nb - 1; j >= 0; --j) {
             const float m = mp[j * kTileFrames];
             top = tmax(top, float_bits(m));
             a += nonneg_to_double_biased(m); b += a; q += b;
             if (has_next) fx += tmax(mp[j * kTileFrames + 1] - m, 0.f);
-            if (sb) sb[j] = m;
           }
         }
         if (top > 0x7f7fffffu) a = b = q = (double)bits_float(0x7fc00000u);   // an infinite / NaN magnitude poisons the frame
@@ -419,10 +414,11 @@ struct AcousticTileKernel {
         }
         float* dst = meldb + (it.row0 + it.f0) * kAcMel;
         for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
-        // boundary spectra: first valid frame, last valid frame (the same frame when the tile holds only one)
+        // boundary spectra: magnitudes of the first and the last valid frame (the same frame when the tile holds
+        // only one), straight from the stage-2 output (514 bank-conflicted words per tile, off the critical path)
         for (int i = tid; i < 2 * kBins; i += kThreads) {
           const int second = i >= kBins, k = i - second * kBins;
-          boundary[(it.item * 2 + second) * kBoundary + k] = sBnd[((second && it.nvalid > 1) ? kBoundary : 0) + k];
+          boundary[(it.item * 2 + second) * kBoundary + k] = sM[k * kTileFrames + (second ? it.nvalid - 1 : 0)];
         }
       } break;
     }
