@@ -493,24 +493,36 @@ struct AcousticMfccKernel {
     float* sC = sD + kTileFrames * kRow;         // [4][13][32] partial dot products
     float* sV = sC + kWarps * kMfcc * 32;        // [13][32] coefficients
     float* sX = sV + kMfcc * 32;                 // [128] boundary flux partials
-    if (ph == 0) {        // clamp at max - 80 dB while staging the tile (coalesced 128-bit loads)
+    if (ph == 0) {        // clamp at max - 80 dB while staging the tile (coalesced 128-bit loads, all issued first:
+                          // one load per loop round left the phase bound by the L2 / DRAM round trip)
       const float4* src = reinterpret_cast<const float4*>(meldb + (it.row0 + it.f0) * kAcMel);
       const int nq = it.nvalid * (kAcMel / 4);
-      for (int i = tid; i < kTileFrames * (kAcMel / 4); i += kThreads) {
-        float4 v = float4{0.f, 0.f, 0.f, 0.f};
-        if (i < nq) {
-          v = src[i];
-          v.x = tmax(v.x, it.cut); v.y = tmax(v.y, it.cut); v.z = tmax(v.z, it.cut); v.w = tmax(v.w, it.cut);
-        }
-        *reinterpret_cast<float4*>(sD + (i >> 5) * kRow + (i & 31) * 4) = v;
+      constexpr int kRounds = kTileFrames * (kAcMel / 4) / kThreads;     // 8
+      float4 v[kRounds];
+#pragma unroll
+      for (int j = 0; j < kRounds; ++j) {
+        const int i = tid + kThreads * j;
+        v[j] = (i < nq) ? ldcg4(src + i) : float4{0.f, 0.f, 0.f, 0.f};
       }
       // spectral flux across the tile boundary: relu(first frame of tile+1 - last frame of this tile)
-      float fl = 0.f;
-      if (it.has_next) {
-        const float* last = boundary + it.item * 2 * kBoundary + kBoundary;
-        const float* first = boundary + (it.item + 1) * 2 * kBoundary;
-        for (int q = tid; q < kBins; q += kThreads) fl += tmax(first[q] - last[q], 0.f);
+      float b0[3], b1[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int q = tid + kThreads * j;
+        const bool on = it.has_next && q < kBins;
+        b0[j] = on ? ldg(boundary + (it.item + 1) * 2 * kBoundary + q) : 0.f;
+        b1[j] = on ? ldg(boundary + it.item * 2 * kBoundary + kBoundary + q) : 0.f;
       }
+#pragma unroll
+      for (int j = 0; j < kRounds; ++j) {
+        const int i = tid + kThreads * j;
+        float4 c = v[j];
+        if (i < nq) { c.x = tmax(c.x, it.cut); c.y = tmax(c.y, it.cut); c.z = tmax(c.z, it.cut); c.w = tmax(c.w, it.cut); }
+        *reinterpret_cast<float4*>(sD + (i >> 5) * kRow + (i & 31) * 4) = c;
+      }
+      float fl = 0.f;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) fl += tmax(b0[j] - b1[j], 0.f);
       sX[tid] = fl;
     } else if (ph == 1) {
       const int f = tid & 31;

@@ -77,19 +77,32 @@ AFE_HD void fbank_mean_den(double s, double ss, int n, float& mean_out, float& d
 AFE_HD void fbank_normalise_plane(float* feat, int32_t* mask, int64_t row0, int tp, int n, const float* stat,
                                   float padding_value, int tid, int nthreads, int64_t q0, int64_t q1) {
   constexpr int kQ = kMel / 4;     // 20 words per frame
+  constexpr int kU = 4;            // words in flight per thread: the loads of a round are issued before its stores
+                                   // (one load per round left the loop bound by the L2 round trip)
   float4* base = reinterpret_cast<float4*>(feat + row0 * kMel);
-  for (int64_t i4 = q0 + tid; i4 < q1; i4 += nthreads) {
-    const int64_t t = i4 / kQ;
-    const int m4 = (int)(i4 - t * kQ);
-    float4 y = float4{padding_value, padding_value, padding_value, padding_value};
-    if (t < n) {
-      const float4 x = ldcg4(base + i4);
-      const float* st = stat + 8 * m4;
-      y.x = (x.x - st[0]) / st[1]; y.y = (x.y - st[2]) / st[3];
-      y.z = (x.z - st[4]) / st[5]; y.w = (x.w - st[6]) / st[7];
+  for (int64_t r4 = q0 + tid; r4 < q1; r4 += (int64_t)kU * nthreads) {
+    float4 x[kU];
+    int64_t t[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t i4 = r4 + (int64_t)u * nthreads;
+      t[u] = i4 / kQ;
+      x[u] = (i4 < q1 && t[u] < n) ? ldcg4(base + i4) : float4{0.f, 0.f, 0.f, 0.f};
     }
-    base[i4] = y;
-    if (m4 == 0 && (t & 1)) mask[(row0 >> 1) + (t >> 1)] = (t < n) ? 1 : 0;
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t i4 = r4 + (int64_t)u * nthreads;
+      if (i4 >= q1) break;
+      const int m4 = (int)(i4 - t[u] * kQ);
+      float4 y = float4{padding_value, padding_value, padding_value, padding_value};
+      if (t[u] < n) {
+        const float* st = stat + 8 * m4;
+        y.x = (x[u].x - st[0]) / st[1]; y.y = (x[u].y - st[2]) / st[3];
+        y.z = (x[u].z - st[4]) / st[5]; y.w = (x[u].w - st[6]) / st[7];
+      }
+      base[i4] = y;
+      if (m4 == 0 && (t[u] & 1)) mask[(row0 >> 1) + (t[u] >> 1)] = (t[u] < n) ? 1 : 0;
+    }
   }
   (void)tp;
 }

@@ -525,12 +525,15 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
       }
     }
   } else {
-    for (long block = 0; block < grid; ++block)
+    for (long block = 0; block < grid; ++block) {
+      if constexpr (has_block_init<K>::value)
+        for (int tid = 0; tid < K::kThreads; ++tid) k.block_init(smem, tid);
       for (long item = block; item < n; item += grid) {
         typename K::Item ic = k.prepare(item);
         for (int ph = 0; ph < K::kPhases; ++ph)
           for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
       }
+    }
   }
   return 0;
 }
