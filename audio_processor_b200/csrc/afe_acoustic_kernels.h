@@ -188,12 +188,18 @@ struct AcousticTileKernel {
     switch (ph) {
       case 0: {   // stage y[reflect(160 f0 - 200 + i)] (edge tiles; interior tiles arrive by TMA)
         const int64_t g0 = (int64_t)it.f0 * kHop - 200;
-        for (int i = tid; i < kAcRaw; i += kThreads) {
-          int64_t g = g0 + i;
+        constexpr int kRounds = (kAcRaw + kThreads - 1) / kThreads;     // 11 loads in flight, then the stores
+        float v[kRounds];
+#pragma unroll
+        for (int j = 0; j < kRounds; ++j) {
+          int64_t g = g0 + tid + kThreads * j;
           if (g < 0) g = -g;
           if (g >= it.L) g = 2 * (it.L - 1) - g;
-          raw[i] = (g >= 0 && g < it.L) ? it.wave[g] : 0.f;
+          v[j] = (tid + kThreads * j < kAcRaw && g >= 0 && g < it.L) ? ldg(it.wave + g) : 0.f;
         }
+#pragma unroll
+        for (int j = 0; j < kRounds; ++j)
+          if (tid + kThreads * j < kAcRaw) raw[tid + kThreads * j] = v[j];
       } break;
       case 1: {   // padded copy for the STFT + 16-sample partials of the unfold frames
         {         // 128-bit loads; the four words of chunk v land at 4 v + (v >> 3) + e (conflict-free both ways)

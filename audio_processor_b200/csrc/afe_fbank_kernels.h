@@ -61,23 +61,26 @@ struct MelTables {
 
 constexpr int kMelIv = kMel + 1;                  // 81 intervals
 
-// (mean, denominator) of one mel bin from its float64 sum and sum of squares over n frames --
+// (mean, 1 / denominator) of one mel bin from its float64 sum and sum of squares over n frames --
+// the reciprocal is formed once per (utterance, bin) so that the normalisation of the utterance's T x 80 values
+// is a subtract and a multiply (within 1.5 ulp of the reference's divide; the contract is 1e-3 absolute) --
 // numpy's mean / var(ddof=1) / sqrt(var + 1e-7) of feature_extraction_seamless_m4t.py:283-288
 AFE_HD void fbank_mean_den(double s, double ss, int n, float& mean_out, float& den_out) {
   const double mean = s / (double)n;
   const double var = (ss - s * mean) / (double)(n - 1);      // ddof = 1; n == 1 -> 0/0 = NaN
   const float varf = (float)var;
   mean_out = (float)mean;
-  den_out = std::sqrt(varf + 1e-7f);
+  den_out = 1.f / std::sqrt(varf + 1e-7f);
 }
 
-// in-place (x - mean) / den over 128-bit words [q0, q1) of one utterance's (tp x 80) plane, right
+// in-place (x - mean) * (1 / den) over 128-bit words [q0, q1) of one utterance's (tp x 80) plane, right
 // padding with padding_value, stride-2 mask (the ODD frame's bit: mask[j] = (2j+1 < n)).
-// stat = [80][2] (mean, den).  Shared by the fused tail phase and FbankNormKernel.
+// stat = [80][2] (mean, 1 / den).  Shared by the fused tail phase and FbankNormKernel.
+template <int kU>                 // words in flight per thread
 AFE_HD void fbank_normalise_plane(float* feat, int32_t* mask, int64_t row0, int tp, int n, const float* stat,
                                   float padding_value, int tid, int nthreads, int64_t q0, int64_t q1) {
   constexpr int kQ = kMel / 4;     // 20 words per frame
-  constexpr int kU = 4;            // words in flight per thread: the loads of a round are issued before its stores
+                                   // kU: the loads of a round are issued before its stores
                                    // (one load per round left the loop bound by the L2 round trip)
   float4* base = reinterpret_cast<float4*>(feat + row0 * kMel);
   for (int64_t r4 = q0 + tid; r4 < q1; r4 += (int64_t)kU * nthreads) {
@@ -97,8 +100,8 @@ AFE_HD void fbank_normalise_plane(float* feat, int32_t* mask, int64_t row0, int 
       float4 y = float4{padding_value, padding_value, padding_value, padding_value};
       if (t[u] < n) {
         const float* st = stat + 8 * m4;
-        y.x = (x[u].x - st[0]) / st[1]; y.y = (x[u].y - st[2]) / st[3];
-        y.z = (x[u].z - st[4]) / st[5]; y.w = (x[u].w - st[6]) / st[7];
+        y.x = (x[u].x - st[0]) * st[1]; y.y = (x[u].y - st[2]) * st[3];
+        y.z = (x[u].z - st[4]) * st[5]; y.w = (x[u].w - st[6]) * st[7];
       }
       base[i4] = y;
       if (m4 == 0 && (t[u] & 1)) mask[(row0 >> 1) + (t[u] >> 1)] = (t[u] < n) ? 1 : 0;
@@ -116,7 +119,7 @@ template <typename T, int TF> struct FbankSmem {
   static constexpr int kG80 = kG16 / 5;                                             // sums of 80 samples: 2 TF + 3
   static constexpr size_t kSumOff = kRawOff + 2 * kRawBytes;                        // double psum80[kG80] (+ spare)
   static constexpr size_t kAccOff = kSumOff + sizeof(double) * ((kG80 + 2) / 2 * 2);   // double acc[80][2]: running (sum, sum sq)
-  static constexpr size_t kStatOff = kAccOff + sizeof(double) * 160;                // float stat[80][2]: (mean, denominator)
+  static constexpr size_t kStatOff = kAccOff + sizeof(double) * 160;                // float stat[80][2]: (mean, 1 / denominator)
   static constexpr size_t kDOff = kStatOff + sizeof(float) * 160;                   // T[padded tile] | sP + sOut
   static constexpr size_t kDBytesT = sizeof(T) * (kSamples + kSamples / 32 + 8);
   static constexpr size_t kPBytes = sizeof(float) * (kBins * TF);
@@ -388,7 +391,7 @@ template <typename T, int TF = kFbTile> struct FbankKernel {
       } break;
       case 6: {   // tail: normalise the whole utterance in place (its raw rows are this block's own, L2-hot)
         const float* stat = reinterpret_cast<const float*>(smem + S::kStatOff);
-        fbank_normalise_plane(out, mask, it.out_row, it.tp, it.nfr, stat, padding_value, tid, kThreads, 0,
+        fbank_normalise_plane<8>(out, mask, it.out_row, it.tp, it.nfr, stat, padding_value, tid, kThreads, 0,
                               (int64_t)it.tp * (kMel / 4));
       } break;
     }
@@ -403,7 +406,7 @@ struct FbankStatsKernel {
   static constexpr int kPhases = 1;
   BatchDesc d;
   const double* partials;
-  float* stats;            // [B][80][2] = (mean, denominator sqrt(var + 1e-7))
+  float* stats;            // [B][80][2] = (mean, 1 / sqrt(var + 1e-7))
   AFE_PLAIN_ITEM
   AFE_HD long num_items() const { return d.nsel; }
   AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
@@ -428,7 +431,7 @@ struct FbankNormKernel {
   BatchDesc d;
   float* feat;             // [rows][80]
   int32_t* mask;           // [rows/2]
-  const float* stats;      // [B][80][2] = (mean, denominator)
+  const float* stats;      // [B][80][2] = (mean, 1 / denominator)
   float padding_value;
   long items_per_utt;      // ceil(max Tp * 80 / 2048)
   AFE_PLAIN_ITEM
@@ -440,7 +443,7 @@ struct FbankNormKernel {
     const int64_t plane4 = (int64_t)tp * (kMel / 4);
     const int64_t q0 = chunk * (kItemFloats / 4);
     if (q0 >= plane4) return;
-    fbank_normalise_plane(feat, mask, ldg(d.out_row + b), tp, ldg(d.frames + b), stats + (int64_t)b * kMel * 2,
+    fbank_normalise_plane<kItemFloats / 4 / kThreads>(feat, mask, ldg(d.out_row + b), tp, ldg(d.frames + b), stats + (int64_t)b * kMel * 2,
                           padding_value, tid, kThreads, q0, tmin<int64_t>(plane4, q0 + kItemFloats / 4));
   }
 };
