@@ -169,6 +169,22 @@ struct AcousticTileKernel {
     s = (a[0] + a[1]) + (a[2] + a[3]); ss = (q[0] + q[1]) + (q[2] + q[3]);
   }
 
+  // second half of the rolloff of one frame: the bin inside role rc where the cumulative energy (lo_c before the
+  // role's bins) reaches thr; 31.25 Hz per bin.  rc < 0: no bin reaches the threshold (argmax of all-False is 0).
+  AFE_HD static float rolloff_bin(const float* sM, int rc, double lo_c, float thr, int f) {
+    if (rc < 0) return 0.f;
+    const float* mp = sM + (16 * rc) * kTileFrames + f;
+    double acc = lo_c;
+    int below = 0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      acc += nonneg_to_double(mp[j * kTileFrames]);
+      below += ((float)acc < thr) ? 1 : 0;
+    }
+    if (rc == 15) below += ((float)(acc + nonneg_to_double(mp[16 * kTileFrames])) < thr) ? 1 : 0;   // bin 256
+    return 31.25f * (float)(16 * rc + below);
+  }
+
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
     float* raw = reinterpret_cast<float*>(smem + AcSmem::kRawOff + (size_t)it.buf * AcSmem::kRawBytes);
     float* dbuf = reinterpret_cast<float*>(smem + AcSmem::kDOff);
@@ -180,6 +196,9 @@ struct AcousticTileKernel {
     double* part = reinterpret_cast<double*>(smem + AcSmem::kPartOff);  // [0] e  [1] sum m k  [2] sum m k^2, each [role * 33 + f]
     float* fxp = reinterpret_cast<float*>(smem + AcSmem::kFxOff);
     float* red = reinterpret_cast<float*>(smem + AcSmem::kRedOff);
+    float* roll_thr = reinterpret_cast<float*>(smem + AcSmem::kThrOff);                    // [32] rolloff threshold of frame f
+    int* roll_rc = reinterpret_cast<int*>(smem + AcSmem::kThrOff) + 32;                    // [32] role holding the crossing (-1: none)
+    double* roll_lo = reinterpret_cast<double*>(smem + AcSmem::kDsumOff);                  // [32] cumulative energy before that role
     float* pf = reinterpret_cast<float*>(smem + AcSmem::kPfOff);       // [0]=centroid [1]=bandwidth [2]=rolloff [3]=flux [4]=rms [5]=zcr [6]=dbmax
     float* sq16 = keep + AcSmem::kSq;  float* zc16 = keep + AcSmem::kZc;  float* lastx = keep + AcSmem::kLast;
     const int role = tid >> 5, f = tid & 31;
@@ -298,90 +317,77 @@ struct AcousticTileKernel {
           part[idx] = e; part[kPS + idx] = c; part[2 * kPS + idx] = c2; fxp[idx] = fx;
         }
       } break;
-      case 5: {   // per-frame scalars.  Transposed: warp w owns frames 2w, 2w+1; each 16-lane segment is one frame,
-                  // lane r of it holds role r's partials -> reductions over the roles are 4-step shuffle trees and the
-                  // cumulative-energy prefix a 4-step scan; the 16 lanes then share the 16 bins of the crossing role.
-                  // (Float64 sums of float32 magnitudes: the tree and the sequential order agree except where a
-                  // partial sum falls on a float32 rounding boundary of the threshold compare.)
-        const int lane = tid & 31;
-        const int fa = 2 * (tid >> 5) + (lane >> 4), r = lane & 15;
-        const int idx = r * kRS + fa;
-        float cen, bw, roll, fxs, mxs, s, z;
-#if AFE_CUDA && defined(__CUDA_ARCH__)
-        const double e = part[idx], c = part[kPS + idx], c2 = part[2 * kPS + idx];
-        s = sq16[10 * fa + r]; z = zc16[10 * fa + r];
-        if (r < 9) { s += sq16[10 * fa + 16 + r]; z += zc16[10 * fa + 16 + r]; }
-        s = seg16_sum(s); z = seg16_sum(z);
-        fxs = seg16_sum(fxp[idx]); mxs = seg16_max(red[idx]);
-        const double incl = seg16_scan(e, r);                 // cum_energy after role r's bins
-        double lo = __shfl_up_sync(0xffffffffu, incl, 1, 16); // ... before them
-        if (r == 0) lo = 0.0;
-        const double tot = __shfl_sync(0xffffffffu, incl, 15, 16);
-        const double C = seg16_sum(c), C2 = seg16_sum(c2);
-        const float total = (float)tot;                      // cum_energy[-1] (float64 accumulate like ATen's cumsum)
-        const float thr = 0.85f * (total + 1e-8f);
-        const bool lo_below = (r == 0) || ((float)lo < thr);
-        const bool hi_below = ((float)incl < thr);
-        const unsigned cross = (__ballot_sync(0xffffffffu, lo_below && !hi_below) >> (lane & 16)) & 0xffffu;
-        const int rc = cross ? (__ffs((int)cross) - 1) : 15;  // the role whose bins hold the 85 % crossing
-        const double lo_c = __shfl_sync(0xffffffffu, lo, rc, 16);
-        const float* mp = sM + (16 * rc) * kTileFrames + fa;
-        const double pin = seg16_scan(nonneg_to_double(mp[r * kTileFrames]), r);
-        int below = __popc((__ballot_sync(0xffffffffu, (float)(lo_c + pin) < thr) >> (lane & 16)) & 0xffffu);
-        const double p15 = __shfl_sync(0xffffffffu, pin, 15, 16);
-        if (rc == 15)                                        // role 15 has 17 bins: bin 256
-          below += ((float)(lo_c + (p15 + nonneg_to_double(mp[16 * kTileFrames]))) < thr) ? 1 : 0;
-        roll = cross ? 31.25f * (float)(16 * rc + below) : 0.f;   // no bin reaches the threshold: argmax of all-False is 0
-#else
-        if (r != 0) break;                                   // host emulation: lane 0 of the segment walks the same trees
-        double ea[16], ca[16], c2a[16], pin[16];
-        float sa[16], za[16], fa16[16], mx = -3.0e38f;
-        for (int q = 0; q < 16; ++q) {
-          const int iq = q * kRS + fa;
-          ea[q] = part[iq]; ca[q] = part[kPS + iq]; c2a[q] = part[2 * kPS + iq];
-          sa[q] = sq16[10 * fa + q]; za[q] = zc16[10 * fa + q];
-          if (q < 9) { sa[q] += sq16[10 * fa + 16 + q]; za[q] += zc16[10 * fa + 16 + q]; }
-          fa16[q] = fxp[iq]; mx = tmax(mx, red[iq]);
-        }
-        s = tree16_sum(sa); z = tree16_sum(za); fxs = tree16_sum(fa16); mxs = mx;
-        scan16(ea);
-        const double tot = ea[15];
-        const double C = tree16_sum(ca), C2 = tree16_sum(c2a);
-        const float total = (float)tot;
-        const float thr = 0.85f * (total + 1e-8f);
-        int rc = -1;
-        for (int q = 0; q < 16 && rc < 0; ++q) {
-          const bool lo_below = (q == 0) || ((float)ea[q - 1] < thr);
-          if (lo_below && !((float)ea[q] < thr)) rc = q;
-        }
-        roll = 0.f;
-        if (rc >= 0) {
-          const double lo_c = rc ? ea[rc - 1] : 0.0;
-          const float* mp = sM + (16 * rc) * kTileFrames + fa;
-          for (int q = 0; q < 16; ++q) pin[q] = nonneg_to_double(mp[q * kTileFrames]);
-          scan16(pin);
-          int below = 0;
-          for (int q = 0; q < 16; ++q) below += ((float)(lo_c + pin[q]) < thr) ? 1 : 0;
-          if (rc == 15) below += ((float)(lo_c + (pin[15] + nonneg_to_double(mp[16 * kTileFrames]))) < thr) ? 1 : 0;
-          roll = 31.25f * (float)(16 * rc + below);
-        }
-#endif
-        {   // centroid and bandwidth from the three moments
-          const float energy = total + 1e-8f;
-          cen = fast_div(31.25f * (float)C, energy);
-          // sum m (31.25 k - cen)^2 from the three moments, in float64
-          const double cd = (double)cen;
-          const double num = (31.25 * 31.25) * C2 - 2.0 * 31.25 * cd * C + cd * cd * tot;
-          bw = mag_sqrt(fast_div((float)(num > 0.0 ? num : 0.0), energy));
-        }
-        if (r == 0) {
-          pf[0 * 32 + fa] = cen; pf[1 * 32 + fa] = bw; pf[2 * 32 + fa] = roll; pf[3 * 32 + fa] = fxs;
-          pf[4 * 32 + fa] = mag_sqrt(s * (1.f / 400.f));
-          pf[5 * 32 + fa] = (z - lastx[fa]) * (1.f / 400.f);
-          pf[6 * 32 + fa] = mxs;
+      case 5: {   // per-frame scalars: warp = quantity, lane = frame.  Every warp reads the 16 role partials of its frame
+                  // into registers and reduces them there as fixed trees (tree16_sum / scan16: depth 4, the additions
+                  // of the earlier 16-lane-segment shuffle version, so the same bits); the warps that need the total
+                  // energy re-derive it with the same additions, so no value crosses warps and the phase has no
+                  // shuffles (the shuffle version spent 1 900 cycles per tile on ~900 of them).
+        const int fa = f;
+        if (role == 0 || role == 1) {            // unfold frame fa = 25 groups of 16 samples: sum of squares / sign changes
+          const float* g = ((role == 0) ? sq16 : zc16) + 10 * fa;
+          float v[16];
+#pragma unroll
+          for (int r = 0; r < 16; ++r) v[r] = (r < 9) ? g[r] + g[16 + r] : g[r];
+          const float t = tree16_sum(v);
+          if (role == 0) pf[4 * 32 + fa] = mag_sqrt(t * (1.f / 400.f));
+          else pf[5 * 32 + fa] = (t - lastx[fa]) * (1.f / 400.f);
+        } else if (role == 2 || role == 3) {     // centroid / bandwidth from the three moments
+          double e[16], c[16];
+#pragma unroll
+          for (int r = 0; r < 16; ++r) { e[r] = part[r * kRS + fa]; c[r] = part[kPS + r * kRS + fa]; }
+          const double tot = tree16_sum(e), C = tree16_sum(c);
+          const float energy = (float)tot + 1e-8f;
+          const float cen = fast_div(31.25f * (float)C, energy);
+          if (role == 2) pf[0 * 32 + fa] = cen;
+          else {   // sum m (31.25 k - cen)^2 from the three moments, in float64
+#pragma unroll
+            for (int r = 0; r < 16; ++r) c[r] = part[2 * kPS + r * kRS + fa];
+            const double C2 = tree16_sum(c);
+            const double cd = (double)cen;
+            const double num = (31.25 * 31.25) * C2 - 2.0 * 31.25 * cd * C + cd * cd * tot;
+            pf[1 * 32 + fa] = mag_sqrt(fast_div((float)(num > 0.0 ? num : 0.0), energy));
+          }
+        } else if (role == 4) {                  // rolloff, first half: the role whose bins hold the 85 % crossing of the
+                                                 // cumulative energy (float compare of in-order float64 sums, like ATen's
+                                                 // cumsum against the float32 threshold); the last phase finds the bin
+          double tot = 0.0;
+#pragma unroll
+          for (int r = 0; r < 16; ++r) tot += part[r * kRS + fa];
+          const float thr = 0.85f * ((float)tot + 1e-8f);
+          int rc = -1;
+          double run = 0.0, lo_c = 0.0;
+#pragma unroll
+          for (int r = 0; r < 16; ++r) {         // the same additions again: run == the prefix of tot
+            const double nxt = run + part[r * kRS + fa];
+            if (rc < 0 && !((float)nxt < thr)) { rc = r; lo_c = run; }
+            run = nxt;
+          }
+          roll_thr[fa] = thr; roll_rc[fa] = rc; roll_lo[fa] = lo_c;
+        } else if (role == 5) {                  // in-tile spectral flux
+          float v[16];
+#pragma unroll
+          for (int r = 0; r < 16; ++r) v[r] = fxp[r * kRS + fa];
+          pf[3 * 32 + fa] = tree16_sum(v);
+        } else if (role == 6) {                  // largest dB of the frame
+          float a = red[fa];
+#pragma unroll
+          for (int r = 1; r < 16; ++r) a = tmax(a, red[r * kRS + fa]);
+          pf[6 * 32 + fa] = a;
+        } else {                                 // warps 7..15 (otherwise idle here): the tile's mel-dB rows and boundary
+                                                 // spectra go to global memory while the scalar warps work
+          constexpr int kFirst = 7 * 32, kN = kThreads - kFirst;
+          float* dst = meldb + (it.row0 + it.f0) * kAcMel;
+          for (int i = tid - kFirst; i < it.nvalid * kAcMel; i += kN) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
+          // magnitudes of the first and the last valid frame (the same frame when the tile holds only one), straight
+          // from the stage-2 output (514 bank-conflicted words per tile, off the critical path)
+          for (int i = tid - kFirst; i < 2 * kBins; i += kN) {
+            const int second = i >= kBins, k = i - second * kBins;
+            boundary[(it.item * 2 + second) * kBoundary + k] = sM[k * kTileFrames + (second ? it.nvalid - 1 : 0)];
+          }
         }
       } break;
-      case 6: {   // tile record (one warp per statistic, lane = frame, fixed-tree reductions), mel-dB rows
+      case 6: {   // tile record (one warp per statistic, lane = frame, fixed-tree reductions); the rolloff warp first
+                  // finds the crossing bin inside the role phase 5 located
         double* rec = tile_rec + it.item * kTileRec;
         if (role < 8) {
           // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff: (sum, sum sq); 5 flux energy; 6 rms range; 7 max dB
@@ -389,7 +395,7 @@ struct AcousticTileKernel {
           const int src = (role == 0) ? 4 : (role == 1) ? 5 : (role < 5) ? (role - 2) : (role == 5) ? 3 : (role == 6) ? 4 : 6;
           const int n = (role < 2 || role == 6) ? n1 : (role == 5) ? it.nvalid - 1 : it.nvalid;
 #if AFE_CUDA && defined(__CUDA_ARCH__)
-          const double v = (double)pf[src * 32 + f];
+          const double v = (double)((role == 4) ? rolloff_bin(sM, roll_rc[f], roll_lo[f], roll_thr[f], f) : pf[src * 32 + f]);
           if (role < 6) {
             const double x = (f < n) ? v : 0.0;
             const double s = warp_tree_sum(x), ss = warp_tree_sum(x * x);
@@ -407,7 +413,7 @@ struct AcousticTileKernel {
           if (f == 0) {   // host emulation: lane 0 walks the same trees
             double a[32], q[32], mn = 3.0e38, mxv = -3.0e38;
             for (int j = 0; j < 32; ++j) {
-              const double v = (j < n) ? (double)pf[src * 32 + j] : 0.0;
+              const double v = (j >= n) ? 0.0 : (double)((role == 4) ? rolloff_bin(sM, roll_rc[j], roll_lo[j], roll_thr[j], j) : pf[src * 32 + j]);
               a[j] = v; q[j] = v * v;
               if (j < n) { mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv; }
             }
@@ -417,14 +423,6 @@ struct AcousticTileKernel {
             else rec[13] = (double)(float)mxv;
           }
 #endif
-        }
-        float* dst = meldb + (it.row0 + it.f0) * kAcMel;
-        for (int i = tid; i < it.nvalid * kAcMel; i += kThreads) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
-        // boundary spectra: magnitudes of the first and the last valid frame (the same frame when the tile holds
-        // only one), straight from the stage-2 output (514 bank-conflicted words per tile, off the critical path)
-        for (int i = tid; i < 2 * kBins; i += kThreads) {
-          const int second = i >= kBins, k = i - second * kBins;
-          boundary[(it.item * 2 + second) * kBoundary + k] = sM[k * kTileFrames + (second ? it.nvalid - 1 : 0)];
         }
       } break;
     }
