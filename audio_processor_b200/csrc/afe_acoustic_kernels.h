@@ -178,7 +178,7 @@ struct AcousticTileKernel {
     int below = 0;
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      acc += nonneg_to_double(mp[j * kTileFrames]);
+      acc += nonneg_to_double_biased(mp[j * kTileFrames]);      // +0 -> 2^-127: far below any threshold step
       below += ((float)acc < thr) ? 1 : 0;
     }
     if (rc == 15) below += ((float)(acc + nonneg_to_double(mp[16 * kTileFrames])) < thr) ? 1 : 0;   // bin 256
@@ -376,8 +376,12 @@ struct AcousticTileKernel {
         } else {                                 // warps 7..15 (otherwise idle here): the tile's mel-dB rows and boundary
                                                  // spectra go to global memory while the scalar warps work
           constexpr int kFirst = 7 * 32, kN = kThreads - kFirst;
-          float* dst = meldb + (it.row0 + it.f0) * kAcMel;
-          for (int i = tid - kFirst; i < it.nvalid * kAcMel; i += kN) dst[i] = sDb[(i >> 7) * kDbStride + (i & 127)];
+          // rows are 512 bytes, the destination 16-byte aligned: four words per store
+          float4* dst = reinterpret_cast<float4*>(meldb + (it.row0 + it.f0) * kAcMel);
+          for (int i = tid - kFirst; i < it.nvalid * (kAcMel / 4); i += kN) {
+            const float* sp = sDb + (i >> 5) * kDbStride + 4 * (i & 31);
+            dst[i] = float4{sp[0], sp[1], sp[2], sp[3]};
+          }
           // magnitudes of the first and the last valid frame (the same frame when the tile holds only one), straight
           // from the stage-2 output (514 bank-conflicted words per tile, off the critical path)
           for (int i = tid - kFirst; i < 2 * kBins; i += kN) {

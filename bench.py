@@ -142,6 +142,23 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
 
 
+def fp64_roof(frames_per_launch, launch_ms, num_sms, sm_mhz):
+    if not launch_ms or not sm_mhz or a_precision_is_f32():
+        return None
+    inst_per_frame, issue_rate = 283.0, 0.49
+    floor = num_sms * 4 * issue_rate * sm_mhz * 1e6 / inst_per_frame          # frames/s at 100 % FP64 issue
+    got = frames_per_launch / (launch_ms * 1e-3)
+    return {"bound": "fp64 issue", "fp64_warp_inst_per_frame": inst_per_frame, "issue_per_clk_per_scheduler": issue_rate,
+            "floor_frames_per_s": floor, "achieved_frames_per_s": got, "frac": got / floor}
+
+
+_PRECISION = ["f64"]
+
+
+def a_precision_is_f32():
+    return _PRECISION[0] == "f32"
+
+
 def ncu_traffic():
     """Per-launch DRAM bytes of the fbank kernel from the committed ncu summary, if any."""
     try:
@@ -175,6 +192,7 @@ def run_afe(a):
     dev_pool = [c.to(dev) for c in pool]
     dev_calls = [dev_pool[i % m] for i in range(a.calls)]
     prec = _native.PRECISION_F64 if a.precision == "f64" else _native.PRECISION_F32
+    _PRECISION[0] = a.precision
     cf = CallFrontend(dev, precision=prec)
     fe = cf.fe
     audio_hours_per_step = a.calls * a.call_seconds / 3600.0
@@ -300,6 +318,9 @@ def run_afe(a):
                          "algorithmic_bytes_per_launch": frames_per_launch * FBANK_BYTES_PER_FRAME,
                          "launches_timed": fb_n, "avg_launch_ms": fb_ms / max(fb_n, 1),
                          "note": "fp64-issue-bound, not HBM-bound: see DESIGN.md section 5"},
+            # the pipe that actually bounds the kernel: 283 FP64 warp-instructions per frame at the
+            # measured 0.49 warp-instructions/clk/scheduler (profiles/r01_pipe_probe_b200.txt), 4 schedulers x SMs
+            "roofline_fp64": fp64_roof(frames_per_launch, fb_ms / max(fb_n, 1), fe.num_sms, clocks.get("sm_mhz")),
             "roofline_other_kernels": other,
         }
         if world == 1 and not a.no_cpu_baseline:
