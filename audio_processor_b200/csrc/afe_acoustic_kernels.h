@@ -453,7 +453,7 @@ struct AcousticMaxKernel {
 };
 
 // One item = one 32-frame tile; 4 warps, lane = frame, warp w owns mel bins [32w, 32w+32).
-// The DCT coefficients are immediates of generated straight-line FFMAs (afe_mel_gen.h; sm_100
+// The DCT coefficients are immediates of generated straight-line FFMAs (afe_dct_gen.h; sm_100
 // has no constant-bank ALU operands, a table in the parameters costs one LDCU per FFMA): per
 // frame 128 shared loads (as 128-bit words) and 13 x 128 FFMAs, no table loads.
 struct AcousticMfccKernel {

@@ -48,10 +48,6 @@ struct afe_ctx {
   float* d_dct = nullptr;                                       // [13][128]
   std::vector<float> h_dct;                                     // host copy: rides in the MFCC kernel's parameters
   float log_floor = 0.f;
-  struct MelDev { const float* up; const float* dn; const int32_t* iv_start; const int32_t* iv_count; const int32_t* role_iv; };
-  MelDev kaldi_mel_dev{}, htk_mel_dev{};
-  struct MelIvPtr { const afe::MelIvOp* ops; const int32_t* role_op; };
-  MelIvPtr kaldi_iv{}, htk_iv{};                                 // table-driven banks (afe_mel_loop.h)
   struct MelSlotPtr { const float* w; const int32_t* start; };   // slot-form banks (afe_mel_slots.h): [16][40], [16][8]
   MelSlotPtr kaldi_slots{}, htk_slots{};
   std::mutex mu;

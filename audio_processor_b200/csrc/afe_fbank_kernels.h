@@ -12,7 +12,7 @@
 // TF = 32 stays.  Linear path (pre-emphasis, DC removal, window, FFT) in T; power / mel / log
 // in float.
 #pragma once
-#include "afe_mel_gen.h"
+#include "afe_dct_gen.h"
 #include "afe_mel_slots.h"
 #include "afe_rfft512.h"
 #include "afe_tables.h"
@@ -51,15 +51,6 @@ AFE_HD void locate_tile(const BatchDesc& d, long item, int& b, int& t) {
   b = lo;
   t = (int)(item - ldg(d.tile_prefix + lo));
 }
-
-// interval-form triangular bank on the device (afe_tables.h SparseBank::up/dn/iv_*)
-struct MelTables {
-  const float* up; const float* dn;               // [257]
-  const int32_t* iv_start; const int32_t* iv_count;   // [F+1]
-  const int32_t* role_iv;                         // [17]
-};
-
-constexpr int kMelIv = kMel + 1;                  // 81 intervals
 
 // (mean, 1 / denominator) of one mel bin from its float64 sum and sum of squares over n frames --
 // the reciprocal is formed once per (utterance, bin) so that the normalisation of the utterance's T x 80 values

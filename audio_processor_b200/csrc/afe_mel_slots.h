@@ -1,7 +1,7 @@
 // afe_mel_slots.h -- triangular mel banks in SLOT form: one straight-line routine shared by all 16 roles.
 //
 // Why: a phase of these block programs runs once per tile, so its code is cold every time.  The generated
-// role-specialised banks (afe_mel_gen.h, 16 code paths, 28-33 KB of SASS) made the loop body of the tile
+// role-specialised banks (one generated code path per role, 28-33 KB of SASS) made the loop body of the tile
 // kernels 50-60 KB -- more than the SM's 32 KB instruction cache -- and ncu showed 31-48 % of the mel phases'
 // samples as no-instruction stalls.  Here filter (role r, slot s) is m = 16 s + (s even ? r : 15 - r) (a zigzag:
 // filter widths grow with m, so every role gets the same work), every slot is padded to the widest filter of

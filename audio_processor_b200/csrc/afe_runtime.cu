@@ -240,10 +240,6 @@ int afe_create(int device, afe_ctx** out) {
     SparseBank mel = make_kaldi_mel_bank();
     ok = ok && (c->d_mel_start = c->upload(mel.start)) && (c->d_mel_count = c->upload(mel.count)) &&
          (c->d_mel_offset = c->upload(mel.offset)) && (c->d_mel_w = c->upload(mel.w));
-    ok = ok && (c->kaldi_mel_dev.up = c->upload(mel.up)) && (c->kaldi_mel_dev.dn = c->upload(mel.dn)) &&
-         (c->kaldi_mel_dev.iv_start = c->upload(mel.iv_start)) && (c->kaldi_mel_dev.iv_count = c->upload(mel.iv_count)) &&
-         (c->kaldi_mel_dev.role_iv = c->upload(mel.role_iv));
-    { const MelIvOps mo = make_mel_iv_ops(mel); ok = ok && (c->kaldi_iv.ops = c->upload(mo.ops)) && (c->kaldi_iv.role_op = c->upload(mo.role_op)); }
     { const MelSlots ms = make_mel_slots(mel, kKaldiSlotLen, 5);
       if (!ms.ok) note_error("afe_create", "Kaldi mel bank does not fit the kernels' slot lengths");
       ok = ok && ms.ok && (c->kaldi_slots.w = c->upload(ms.w)) && (c->kaldi_slots.start = c->upload(ms.start)); }
@@ -254,10 +250,6 @@ int afe_create(int device, afe_ctx** out) {
     SparseBank htk = make_htk_mel_bank();
     ok = ok && (c->d_htk_start = c->upload(htk.start)) && (c->d_htk_count = c->upload(htk.count)) &&
          (c->d_htk_offset = c->upload(htk.offset)) && (c->d_htk_w = c->upload(htk.w));
-    ok = ok && (c->htk_mel_dev.up = c->upload(htk.up)) && (c->htk_mel_dev.dn = c->upload(htk.dn)) &&
-         (c->htk_mel_dev.iv_start = c->upload(htk.iv_start)) && (c->htk_mel_dev.iv_count = c->upload(htk.iv_count)) &&
-         (c->htk_mel_dev.role_iv = c->upload(htk.role_iv));
-    { const MelIvOps mo = make_mel_iv_ops(htk); ok = ok && (c->htk_iv.ops = c->upload(mo.ops)) && (c->htk_iv.role_op = c->upload(mo.role_op)); }
     { const MelSlots ms = make_mel_slots(htk, kHtkSlotLen, 8);
       if (!ms.ok) note_error("afe_create", "HTK mel bank does not fit the kernels' slot lengths");
       ok = ok && ms.ok && (c->htk_slots.w = c->upload(ms.w)) && (c->htk_slots.start = c->upload(ms.start)); }

@@ -183,23 +183,6 @@ std::vector<float> make_dct_matrix() {
 }
 
 
-MelIvOps make_mel_iv_ops(const SparseBank& b) {
-  MelIvOps out;
-  out.role_op.assign(17, 0);
-  for (int r = 0; r < 16; ++r) {
-    out.role_op[(size_t)r] = (int32_t)out.ops.size();
-    for (int i = b.role_iv[(size_t)r]; i < b.role_iv[(size_t)r + 1]; ++i) {
-      const int k0 = b.iv_start[(size_t)i], n = b.iv_count[(size_t)i];
-      if (n == 0) { out.ops.push_back(MelIvOp{0.f, 0.f, 0, i}); continue; }
-      for (int k = k0; k < k0 + n; ++k)
-        out.ops.push_back(MelIvOp{b.up[(size_t)k], b.dn[(size_t)k], k, (k == k0 + n - 1) ? i : -1});
-    }
-    while ((out.ops.size() - (size_t)out.role_op[(size_t)r]) % 4 != 0) out.ops.push_back(MelIvOp{0.f, 0.f, 0, -1});
-  }
-  out.role_op[16] = (int32_t)out.ops.size();
-  return out;
-}
-
 MelSlots make_mel_slots(const SparseBank& b, const int* slot_len, int nslots) {
   MelSlots out;
   out.w.assign((size_t)16 * kMelSlotRow, 0.f);

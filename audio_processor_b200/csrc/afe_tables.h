@@ -46,17 +46,6 @@ struct SparseBank {
 SparseBank make_kaldi_mel_bank();        // 80 filters, 20..8000 Hz, mel-space triangles
 SparseBank make_htk_mel_bank();          // 128 filters, 0..8000 Hz, Hz-space triangles (float32 like torchaudio)
 
-// The interval form as one op per bin for the table-driven device loop (afe_mel_loop.h): role r owns the
-// intervals [role_iv[r], role_iv[r+1]) and walks ops [role_op[r], role_op[r+1]) (a multiple of 4):
-//   u = fma(wu, P[bin], u);  d = fma(wd, P[bin], d);  if (end >= 0) { U[end] = u; D[end] = d; u = d = 0; }
-// An interval without bins is one op with zero weights; padding ops have zero weights and end = -1.
-struct MelIvOp { float wu, wd; int32_t bin; int32_t end; };
-struct MelIvOps {
-  std::vector<MelIvOp> ops;
-  std::vector<int32_t> role_op;          // [17]
-};
-MelIvOps make_mel_iv_ops(const SparseBank& bank);
-
 // Slot form for the device (afe_mel_slots.h): filter (role r, slot s) = 16 s + (s even ? r : 15 - r); slot s is
 // padded to slot_len[s] bins (zero weights; the first bin moves down where the padding would pass bin 256).
 // w[16][kMelSlotRow] rows of weights, slots back to back; start[16][kMelSlotStarts] first bin of every slot.
