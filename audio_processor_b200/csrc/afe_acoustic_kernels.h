@@ -376,11 +376,16 @@ struct AcousticTileKernel {
         } else {                                 // warps 7..15 (otherwise idle here): the tile's mel-dB rows and boundary
                                                  // spectra go to global memory while the scalar warps work
           constexpr int kFirst = 7 * 32, kN = kThreads - kFirst;
-          // rows are 512 bytes, the destination 16-byte aligned: four words per store
-          float4* dst = reinterpret_cast<float4*>(meldb + (it.row0 + it.f0) * kAcMel);
-          for (int i = tid - kFirst; i < it.nvalid * (kAcMel / 4); i += kN) {
-            const float* sp = sDb + (i >> 5) * kDbStride + 4 * (i & 31);
-            dst[i] = float4{sp[0], sp[1], sp[2], sp[3]};
+          // (scalar on purpose: 128-bit stores fed by four bank-conflicted loads measured slower); five loads in
+          // flight per round
+          float* dst = meldb + (it.row0 + it.f0) * kAcMel;
+          const int total = it.nvalid * kAcMel;
+          for (int i0 = tid - kFirst; i0 < total; i0 += 5 * kN) {
+            float v[5];
+#pragma unroll
+            for (int u = 0; u < 5; ++u) { const int i = i0 + u * kN; v[u] = (i < total) ? sDb[(i >> 7) * kDbStride + (i & 127)] : 0.f; }
+#pragma unroll
+            for (int u = 0; u < 5; ++u) { const int i = i0 + u * kN; if (i < total) dst[i] = v[u]; }
           }
           // magnitudes of the first and the last valid frame (the same frame when the tile holds only one), straight
           // from the stage-2 output (514 bank-conflicted words per tile, off the critical path)
