@@ -233,33 +233,60 @@ struct AcousticTileKernel {
             }
           }
         }
-        if (tid < kGroups16) {
+        if ((tid >> 5) <= (kGroups16 - 1) >> 5) {     // warps 0..10 (whole warps: the neighbour exchange below is a shuffle)
           // group t = unfold samples [16 t, 16 t + 16) = raw[200 + 16 t ...]: sum of squares and the number of sign
-          // changes over the pairs (i - 1, i) ENDING in the group.  Signs as exact small floats: s = [x > 0] - [x < 0],
-          // n = s^2 = [x != 0]; a pair crosses iff s_a s_c = -1, so crossings = (sum n_a n_c - sum s_a s_c) / 2 -- two
-          // FMAs per pair, no branches, zeros never count (sentiment_analysis.py:830-832).
-          const int t = tid;
+          // changes over the pairs (i - 1, i) ENDING in the group.  Four 128-bit loads in an order rotated by
+          // rot(t) (conflict-free, see FbankKernel::group16); the sample before the group is the neighbour lane's
+          // last one.  Signs as exact small floats: s = [x > 0] - [x < 0], n = s^2 = [x != 0]; a pair crosses iff
+          // s_a s_c = -1, so crossings = (sum n_a n_c - sum s_a s_c) / 2 -- two FMAs per pair, no branches, zeros
+          // never count (sentiment_analysis.py:830-832).
+          const int t = tmin(tid, kGroups16 - 1);
+          const int rot = ((t >> 1) + 2 * (t & 1)) & 3;
           const float4* g4 = reinterpret_cast<const float4*>(raw + 200 + 16 * t);
-          const float xprev = raw[200 + 16 * t - 1];
-          float sb = ((xprev > 0.f) ? 1.f : 0.f) - ((xprev < 0.f) ? 1.f : 0.f), nb = sb * sb;
-          float sq = 0.f, zn = 0.f, zs = 0.f;
-#pragma unroll 1
-          for (int q = 0; q < 4; ++q) {          // rolled: the phase runs once per tile, compact code beats ILP here
-            const float4 v = g4[q];
-            const float s0 = ((v.x > 0.f) ? 1.f : 0.f) - ((v.x < 0.f) ? 1.f : 0.f);
-            const float s1 = ((v.y > 0.f) ? 1.f : 0.f) - ((v.y < 0.f) ? 1.f : 0.f);
-            const float s2 = ((v.z > 0.f) ? 1.f : 0.f) - ((v.z < 0.f) ? 1.f : 0.f);
-            const float s3 = ((v.w > 0.f) ? 1.f : 0.f) - ((v.w < 0.f) ? 1.f : 0.f);
-            const float n0 = s0 * s0, n1 = s1 * s1, n2 = s2 * s2, n3 = s3 * s3;
-            zn = fma_f(nb, n0, zn); zs = fma_f(sb, s0, zs);
-            zn = fma_f(n0, n1, zn); zs = fma_f(s0, s1, zs);
-            zn = fma_f(n1, n2, zn); zs = fma_f(s1, s2, zs);
-            zn = fma_f(n2, n3, zn); zs = fma_f(s2, s3, zs);
-            sq = fma_f(v.x, v.x, sq); sq = fma_f(v.y, v.y, sq); sq = fma_f(v.z, v.z, sq); sq = fma_f(v.w, v.w, sq);
-            sb = s3; nb = n3;
+          float x[4][4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 v = g4[(q + rot) & 3];
+            x[q][0] = v.x; x[q][1] = v.y; x[q][2] = v.z; x[q][3] = v.w;
           }
-          sq16[t] = sq;
-          zc16[t] = 0.5f * (zn - zs);
+          float xprev;
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+          {
+            const float last = (rot == 0) ? x[3][3] : (rot == 1) ? x[2][3] : (rot == 2) ? x[1][3] : x[0][3];   // chunk 3
+            xprev = __shfl_up_sync(0xffffffffu, last, 1);
+            if ((tid & 31) == 0) xprev = raw[200 + 16 * t - 1];
+          }
+#else
+          xprev = raw[200 + 16 * t - 1];
+#endif
+          float sg[4][4], nz[4][4];
+          float sq0 = 0.f, sq1 = 0.f, sq2 = 0.f, sq3 = 0.f;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              sg[q][e] = ((x[q][e] > 0.f) ? 1.f : 0.f) - ((x[q][e] < 0.f) ? 1.f : 0.f);
+              nz[q][e] = sg[q][e] * sg[q][e];
+            }
+            sq0 = fma_f(x[q][0], x[q][0], sq0); sq1 = fma_f(x[q][1], x[q][1], sq1);
+            sq2 = fma_f(x[q][2], x[q][2], sq2); sq3 = fma_f(x[q][3], x[q][3], sq3);
+          }
+          const float sprev = ((xprev > 0.f) ? 1.f : 0.f) - ((xprev < 0.f) ? 1.f : 0.f), nprev = sprev * sprev;
+          float zn0 = 0.f, zs0 = 0.f, zn1 = 0.f, zs1 = 0.f;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int cq = (q + rot) & 3;                         // chunk held by slot q; slot q - 1 holds chunk cq - 1
+            const float sb = (cq == 0) ? sprev : sg[(q + 3) & 3][3];
+            const float nb = (cq == 0) ? nprev : nz[(q + 3) & 3][3];
+            zn0 = fma_f(nb, nz[q][0], zn0);       zs0 = fma_f(sb, sg[q][0], zs0);
+            zn1 = fma_f(nz[q][0], nz[q][1], zn1); zs1 = fma_f(sg[q][0], sg[q][1], zs1);
+            zn0 = fma_f(nz[q][1], nz[q][2], zn0); zs0 = fma_f(sg[q][1], sg[q][2], zs0);
+            zn1 = fma_f(nz[q][2], nz[q][3], zn1); zs1 = fma_f(sg[q][2], sg[q][3], zs1);
+          }
+          if (tid < kGroups16) {
+            sq16[t] = (sq0 + sq1) + (sq2 + sq3);
+            zc16[t] = 0.5f * ((zn0 + zn1) - (zs0 + zs1));
+          }
         }
         if (tid < kTileFrames)     // the pair (-1, 0) of unfold frame tid is counted by its first group but is NOT part of the frame
           lastx[tid] = crossing(raw[200 + kHop * tid - 1], raw[200 + kHop * tid]) ? 1.f : 0.f;
