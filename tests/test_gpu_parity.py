@@ -314,3 +314,29 @@ def test_call_frontend_pcm16_ingest_is_bit_identical(fe):
     c = cf.process_calls([p16], 16000)
     d = cf.process_calls([p16.to(torch.float32) / 32768.0], 16000)
     assert torch.equal(c.features["stereo"][0][0], d.features["stereo"][0][0])
+
+
+def test_repeated_runs_are_bit_identical(fe):
+    """Race / ordering check in place of compute-sanitizer (closed on this pool): every kernel's reductions are
+    fixed trees or in-order sums and no shared word is written by two threads inside a phase, so the same batch --
+    ragged segments through fbank and the four acoustic kernels, interleaved with other work on the device --
+    must give the same bits every time."""
+    import torch
+    from audio_processor_b200 import acoustic, synth
+    segs = [synth.speech_like(n, 16000, 40 + i).to(fe.device)
+            for i, n in enumerate((8000, 16001, 47999, 131072, 400, 5359, 5360, 5361, 400000, 123457))]
+    noise = torch.empty(64 << 20, dtype=torch.uint8, device=fe.device)
+    ref = None
+    for rep in range(6):
+        noise.random_(0, 255)                                   # different L2 / scheduling state each time
+        feat, mask = fe.fbank(segs)
+        rows = acoustic.extract_acoustic_features_batch([s.unsqueeze(0) for s in segs], 16000, fe.device)
+        got = (feat.clone(), mask.clone(), [tuple(d.values()) for d in rows])
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = got
+            continue
+        assert torch.equal(ref[0].view(torch.int32), got[0].view(torch.int32))     # bit patterns (NaN-safe)
+        assert torch.equal(ref[1], got[1])
+        assert all(np.array_equal(np.asarray(a, np.float64), np.asarray(b, np.float64), equal_nan=True)
+                   for a, b in zip(ref[2], got[2]))
