@@ -474,13 +474,22 @@ struct AcousticMaxKernel {
   AFE_HD long num_items() const { return d.B; }
   AFE_HD void phase(int, const Item& it, unsigned char*, int tid) const {
     const long item = it.item;
-    if (tid != 0) return;
+    const long t0 = ldg(d.tile_prefix + item), t1 = ldg(d.tile_prefix + item + 1);
     double mx = -3.0e38;
-    for (long t = ldg(d.tile_prefix + item); t < ldg(d.tile_prefix + item + 1); ++t) {
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+    for (long t = t0 + tid; t < t1; t += kThreads) {       // lane-strided: the loads of a waveform's tiles are in flight together
       const double v = tile_rec[t * kTileRec + 13];
       mx = v > mx ? v : mx;
     }
-    gmax[item] = (float)mx;
+    mx = warp_tree_max(mx);
+#else
+    if (tid != 0) return;
+    for (long t = t0; t < t1; ++t) {
+      const double v = tile_rec[t * kTileRec + 13];
+      mx = v > mx ? v : mx;
+    }
+#endif
+    if (tid == 0) gmax[item] = (float)mx;
   }
 };
 
