@@ -620,6 +620,16 @@ struct AcousticFinalKernel {
     const double period = max_lag > 0 ? (double)(max_lag * hop) / 16000.0 : 0.0;
     return period > 0.0 ? 60.0 / period : 0.0;
   }
+  // s += p[t * stride], ss += p[t * stride + 1] for t in [t0, t1), in tile order, eight tiles' loads in flight
+  AFE_HD static void sum_pairs(const double* p, int stride, long t0, long t1, double& s, double& ss) {
+    for (long t = t0; t < t1; t += 8) {
+      double a[8], b[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { const bool on = t + u < t1; a[u] = on ? p[(t + u) * stride] : 0.0; b[u] = on ? p[(t + u) * stride + 1] : 0.0; }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) if (t + u < t1) { s += a[u]; ss += b[u]; }
+    }
+  }
   AFE_HD static void mean_std(double s, double ss, int n, float& mean, float& sd) {
     const double m = s / (double)n;
     mean = (float)m;
@@ -655,11 +665,15 @@ struct AcousticFinalKernel {
     if (tid == 0) status[orow] = 0;
     if (tid < 5) {              // rms, zcr over F1 frames; centroid, bandwidth, rolloff over F2
       double s = 0.0, ss = 0.0, mn = 3.0e38, mx = -3.0e38;
-      for (long t = t0; t < t1; ++t) {
-        s += tile_rec[t * kTileRec + 2 * tid]; ss += tile_rec[t * kTileRec + 2 * tid + 1];
-        if (tid == 0) {
-          const double a = tile_rec[t * kTileRec + 11], c = tile_rec[t * kTileRec + 12];
-          mn = a < mn ? a : mn; mx = c > mx ? c : mx;
+      sum_pairs(tile_rec + 2 * tid, kTileRec, t0, t1, s, ss);
+      if (tid == 0) {
+        // min / max of the per-tile rms extremes, batched the same way
+        for (long t = t0; t < t1; t += 8) {
+          double a[8], c[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) { const bool on = t + u < t1; a[u] = on ? tile_rec[(t + u) * kTileRec + 11] : 3.0e38; c[u] = on ? tile_rec[(t + u) * kTileRec + 12] : -3.0e38; }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) { mn = a[u] < mn ? a[u] : mn; mx = c[u] > mx ? c[u] : mx; }
         }
       }
       float mean, sd;
@@ -669,12 +683,18 @@ struct AcousticFinalKernel {
       if (tid == 0) o[2] = (float)(mx - mn);
     } else if (tid == 5) {      // spectral-flux energy: in-tile pairs + tile-boundary pairs
       double s = 0.0;
-      for (long t = t0; t < t1; ++t) s += tile_rec[t * kTileRec + 10] + mfcc_rec[(t * 14 + 13) * 2];
+      for (long t = t0; t < t1; t += 8) {      // eight tiles' loads in flight, added in tile order
+        double a[8], c[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { const bool on = t + u < t1; a[u] = on ? tile_rec[(t + u) * kTileRec + 10] : 0.0; c[u] = on ? mfcc_rec[((t + u) * 14 + 13) * 2] : 0.0; }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) if (t + u < t1) s += a[u] + c[u];
+      }
       o[11] = (float)s;
     } else if (tid >= 6 && tid < 6 + kMfcc) {
       const int c = tid - 6;
       double s = 0.0, ss = 0.0;
-      for (long t = t0; t < t1; ++t) { s += mfcc_rec[(t * 14 + c) * 2]; ss += mfcc_rec[(t * 14 + c) * 2 + 1]; }
+      sum_pairs(mfcc_rec + 2 * c, 28, t0, t1, s, ss);
       float mean, sd;
       mean_std(s, ss, F2, mean, sd);
       o[12 + 2 * c] = mean; o[13 + 2 * c] = sd;
