@@ -52,7 +52,7 @@ struct AcSmem {
   static constexpr size_t kMOff = kPOff + sizeof(float) * kBins * kTileFrames;           // float sM[257*32] magnitude
   static constexpr size_t kExOff = (kMOff + sizeof(float) * kBins * kTileFrames + 15) / 16 * 16;
   // the exchange region after stage 2: sDb[32][129] | double part[3][16][33] | float fx,red [16][33] | pf[8][32]
-  // (role stride 33: lane = frame writes AND lane = role reads of phase 5 are both conflict-free)
+  // (role stride 33: odd, so lane = frame accesses of a role row are conflict-free whatever the row)
   static constexpr int kRS = 33, kPS = 16 * kRS;
   static constexpr size_t kDbOff = kExOff;
   static constexpr size_t kPartOff = (kDbOff + sizeof(float) * kTileFrames * kDbStride + 15) / 16 * 16;
@@ -60,14 +60,13 @@ struct AcSmem {
   static constexpr size_t kRedOff = kFxOff + sizeof(float) * kPS;
   static constexpr size_t kPfOff = kRedOff + sizeof(float) * kPS;
   static constexpr size_t kThrOff = kPfOff + sizeof(float) * 8 * 32;
-  static constexpr size_t kDsumOff = kThrOff + sizeof(float) * 64;                   // double dsum[3][32]: total, sum m k, sum m k^2
+  static constexpr size_t kDsumOff = kThrOff + sizeof(float) * 64;                   // float thr[32] | int rc[32] at kThrOff, double lo[32] here: the rolloff hand-over
   static constexpr size_t kHannOff = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // float hann[16][26] (block_init)
   static constexpr size_t kTwOff = kHannOff + sizeof(float) * kRoles * kWinRow;               // float tw512[16][16][2]
-  static constexpr size_t kBndOff = kTwOff + sizeof(float) * kRoles * 32;                      // float sBnd[2][260] boundary spectra
-  static constexpr size_t kMelWOff = (kBndOff + sizeof(float) * 2 * kBoundary + 15) / 16 * 16;   // float melw[16][40] slot-form HTK bank (block_init)
+  static constexpr size_t kMelWOff = (kTwOff + sizeof(float) * kRoles * 32 + 15) / 16 * 16;      // float melw[16][40] slot-form HTK bank (block_init)
   static constexpr size_t kMelSOff = kMelWOff + sizeof(float) * kRoles * kMelSlotRow;            // int32 mels[16][8]
   static constexpr size_t kBytes = kMelSOff + sizeof(int32_t) * kRoles * kMelSlotStarts;
-  static_assert(kDsumOff % 8 == 0 && kDsumOff + sizeof(double) * 96 <= kHannOff, "ex region too small");
+  static_assert(kDsumOff % 8 == 0 && kDsumOff + sizeof(double) * 32 <= kHannOff, "ex region too small");
 };
 
 // sqrt for magnitudes: one MUFU (max relative error ~1 ulp); the reference's float32 |X| carries
