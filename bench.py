@@ -177,6 +177,11 @@ def run_afe(a):
     rank, local_rank, world = dist_env()
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # stdout carries exactly ONE line, the JSON result: anything a library writes to fd 1 on the way (NCCL prints
+    # "NCCL version ..." there when NCCL_DEBUG is set) is sent to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -329,9 +334,11 @@ def run_afe(a):
             v, wall, desc = libref.timed_sample(max(1, min(cores, 64)), calls_per_worker=3, seconds=60.0)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": max(1, min(cores, 64)), "kind": "port",
                                     "sample": desc, "wall_s": wall}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
+    os.close(json_fd)
 
 
 def main():
