@@ -60,6 +60,7 @@ class CallFrontend:
         self._tables = {}
         self._plans: Dict[tuple, _Plan] = {}
         self._copy_stream = None
+        self.trace = None        # debug: set to a dict to get CUDA-event timelines of the uploads and sub-batches (tools/e2e_timeline.py)
 
     def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True,
                       sub_batch: Optional[int] = None) -> FrontendResult:
@@ -118,7 +119,7 @@ class CallFrontend:
                         else:
                             xdev[i].copy_(c, non_blocking=True)
                         xs_all[i] = xdev[i]
-                        evs[i] = torch.cuda.Event()
+                        evs[i] = torch.cuda.Event(enable_timing=self.trace is not None)
                         evs[i].record(self._copy_stream)
         else:
             xs_all = [c.to(dev) for c in calls]
@@ -140,9 +141,14 @@ class CallFrontend:
             status = torch.empty((2 * n,), dtype=torch.int32, device=dev)
         res.waveforms = [None] * len(calls)                       # type: ignore[list-item]
         done_prev: Optional[torch.cuda.Event] = None
+        if self.trace is not None:
+            t_start = torch.cuda.Event(enable_timing=True); t_start.record(main)
+            self.trace.update(start=t_start, uploads=evs, groups=[])
         k0 = 0
         while k0 < len(calls):
             k1 = self._next_group(k0, len(calls), evs, groups)
+            if self.trace is not None:
+                g0 = torch.cuda.Event(enable_timing=True); g0.record(main)
             xs = xs_all[k0:k1]
             last_ev = next((evs[i] for i in range(k1 - 1, k0 - 1, -1) if evs[i] is not None), None)
             if last_ev is not None:
@@ -186,6 +192,9 @@ class CallFrontend:
             if self.acoustic:
                 fe.acoustic_ptrs(agent_p + client_p, sub_lens * 2, sr_t, out=rows, status=status,
                                  out_index=list(range(c0, c1)) + list(range(n + c0, n + c1)))
+            if self.trace is not None:
+                g1 = torch.cuda.Event(enable_timing=True); g1.record(main)
+                self.trace["groups"].append((k0, k1, g0, g1))
             if groups is None and k1 < len(calls):
                 # adaptive grouping: at most two groups in flight, so the next group is formed from
                 # what has ARRIVED by the time the GPU is about to need it
