@@ -60,6 +60,7 @@ class CallFrontend:
         self._tables = {}
         self._plans: Dict[tuple, _Plan] = {}
         self._copy_stream = None
+        self._side_stream = None
         self.trace = None        # debug: set to a dict to get CUDA-event timelines of the uploads and sub-batches (tools/e2e_timeline.py)
 
     def process_calls(self, calls: Sequence[torch.Tensor], sample_rate: int, acoustic_to_host: bool = True,
@@ -185,13 +186,26 @@ class CallFrontend:
                 mixed_p.append(m.data_ptr() + 4 * s); agent_p.append(pa + 4 * s); client_p.append(pc + 4 * s)
             sub_lens = lens[c0:c1]
             sub_rows = row_of[c0:c1]
+            # fbank and the acoustic features both read the resampled waveforms and nothing of each other: the
+            # acoustic kernels go to a second stream, so their blocks fill the SMs the fbank kernel's last blocks
+            # leave idle (each tile kernel occupies a whole SM) and the small kernels of the two chains overlap
+            if self.acoustic and self.kTwoStreams:
+                if self._side_stream is None:
+                    self._side_stream = torch.cuda.Stream(dev)
+                side = self._side_stream
+                side.wait_stream(main)                            # the resampled waveforms are ready
             fe.fbank_placed(mixed_p + agent_p + client_p, sub_lens * 3,
                             sub_rows + [r + total_rows for r in sub_rows] + [r + 2 * total_rows for r in sub_rows],
                             tp_of[c0:c1] * 3, feat_all, mask_all, padding_value=self.padding_value,
                             precision=self.precision)
             if self.acoustic:
-                fe.acoustic_ptrs(agent_p + client_p, sub_lens * 2, sr_t, out=rows, status=status,
-                                 out_index=list(range(c0, c1)) + list(range(n + c0, n + c1)))
+                oi = list(range(c0, c1)) + list(range(n + c0, n + c1))
+                if self.kTwoStreams:
+                    with torch.cuda.stream(side):
+                        fe.acoustic_ptrs(agent_p + client_p, sub_lens * 2, sr_t, out=rows, status=status, out_index=oi)
+                    main.wait_stream(side)
+                else:
+                    fe.acoustic_ptrs(agent_p + client_p, sub_lens * 2, sr_t, out=rows, status=status, out_index=oi)
             if self.trace is not None:
                 g1 = torch.cuda.Event(enable_timing=True); g1.record(main)
                 self.trace["groups"].append((k0, k1, g0, g1))
@@ -229,6 +243,7 @@ class CallFrontend:
         return None
 
     kFirstGroup, kMinGroup, kMaxGroup = 2, 4, 16
+    kTwoStreams = True       # acoustic kernels on a second stream beside the fbank kernels
 
     def _next_group(self, k0: int, n_calls: int, evs, groups) -> int:
         """End of the sub-batch that starts at call k0.  Adaptive mode: wait for ``kMinGroup`` calls to
