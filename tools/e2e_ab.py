@@ -2,7 +2,8 @@
 
 Findings of the 11th session (knobs that were experiments only are not in the library): two copy streams 29.5 ms and three
 32.5 ms against 24.8 ms with one (although two streams ALONE copy at 54.8 GB/s against 49.9, tools/h2d_probe.py); copies split
-into 8 MB / 4 MB pieces 25.2 / 25.7 ms against 24.7 ms whole; tapering the last sub-batches: noise.  tools/e2e_timeline.py
+into 8 MB / 4 MB pieces 25.2 / 25.7 ms against 24.7 ms whole; tapering the last sub-batches: noise; with the group's copies
+waited for on every copy stream (second try): two streams 27.2 ms, three 30.5 ms against 24.2 ms.  tools/e2e_timeline.py
 shows why: with 4-call sub-batches the GPU is busy almost all the time (1.2-1.9 ms per 4 calls against 1.55 ms of upload)."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -31,10 +32,9 @@ def run(kind, steps=10):
     return 1e3 * (time.perf_counter() - t0) / steps
 
 
-variants = {"min4 first2 max16": dict(), "min2": dict(kMinGroup=2), "min2 first1": dict(kMinGroup=2, kFirstGroup=1),
-            "min3": dict(kMinGroup=3), "min2 max32": dict(kMinGroup=2, kMaxGroup=32), "min1": dict(kMinGroup=1, kFirstGroup=1)}
-base = dict(kMinGroup=4, kFirstGroup=2, kMaxGroup=16)
-for rnd in range(2):
+variants = {"two streams": dict(), "one stream": dict(kTwoStreams=False)}
+base = dict(kMinGroup=4, kFirstGroup=2, kMaxGroup=16, kTwoStreams=True)
+for rnd in range(3):
     for name, kw in variants.items():
         for k, v in {**base, **kw}.items():
             setattr(CallFrontend, k, v)
