@@ -3,7 +3,8 @@
 Findings of the 11th session (knobs that were experiments only are not in the library): two copy streams 29.5 ms and three
 32.5 ms against 24.8 ms with one (although two streams ALONE copy at 54.8 GB/s against 49.9, tools/h2d_probe.py); copies split
 into 8 MB / 4 MB pieces 25.2 / 25.7 ms against 24.7 ms whole; tapering the last sub-batches: noise; with the group's copies
-waited for on every copy stream (second try): two streams 27.2 ms, three 30.5 ms against 24.2 ms.  tools/e2e_timeline.py
+waited for on every copy stream (second try): two streams 27.2 ms, three 30.5 ms against 24.2 ms; copies enqueued 16
+calls ahead of the launches instead of all 64 first: 17.16 vs 17.30 ms on the wav path, nothing on float32 -- not kept.  tools/e2e_timeline.py
 shows why: with 4-call sub-batches the GPU is busy almost all the time (1.2-1.9 ms per 4 calls against 1.55 ms of upload)."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
