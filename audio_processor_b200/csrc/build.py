@@ -35,11 +35,12 @@ def _stale(target: str) -> bool:
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 
-def build_cuda(force: bool = False, verbose: bool = False, extra=()) -> str:
-    if not force and not _stale(CUDA_LIB):
-        return CUDA_LIB
+def build_cuda(force: bool = False, verbose: bool = False, extra=(), out: str = CUDA_LIB) -> str:
+    """``out`` / ``extra``: development variants (tools/kernel_lab.py builds them under tools/_bin/)."""
+    if not force and not _stale(out):
+        return out
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc, *NVCC_FLAGS, *extra, "-shared", "-o", CUDA_LIB] + [os.path.join(HERE, s) for s in SOURCES]
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-shared", "-o", out] + [os.path.join(HERE, s) for s in SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas"); cmd.insert(2, "-v")
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -47,7 +48,7 @@ def build_cuda(force: bool = False, verbose: bool = False, extra=()) -> str:
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed building libafe.so")
-    return CUDA_LIB
+    return out
 
 
 def build_emu(force: bool = False) -> str:
