@@ -55,7 +55,7 @@ def build_emu(force: bool = False) -> str:
     if not force and not _stale(EMU_LIB):
         return EMU_LIB
     os.makedirs(os.path.dirname(EMU_LIB), exist_ok=True)
-    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DAFE_EMULATE", "-ffp-contract=off", "-o", EMU_LIB]
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DAFE_EMULATE", "-ffp-contract=off", "-o", EMU_LIB] + os.environ.get("AFE_EMU_EXTRA", "").split() + os.environ.get("AFE_EMU_EXTRA", "").split()
     for s in SOURCES:
         cmd += ["-x", "c++", os.path.join(HERE, s)]
     r = subprocess.run(cmd, capture_output=True, text=True)

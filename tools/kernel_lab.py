@@ -95,7 +95,7 @@ def run(a):
                                  env={**os.environ, "AFE_PHASE_TRACE": "1"})
             del os.environ["AFE_PHASE_TRACE"]
             lines = [l for l in sub.stderr.splitlines() if "afe trace" in l]
-            for l in lines[-3:]:
+            for l in lines[-17:]:
                 print("   ", l[:220])
 
 
