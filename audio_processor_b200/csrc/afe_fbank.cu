@@ -47,13 +47,13 @@ FbankLayout fbank_layout(const int64_t* lengths, int B) {
 template <typename T>
 int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, double* partials,
               const T* window, const T* tw, int32_t* mask, float padding_value) {
-  FbankPipeKernel<T> k;
+  FbankKernel<T> k;
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
   k.mask = mask; k.padding_value = padding_value;
   k.log_floor = ctx->log_floor;
   k.mel_w = ctx->kaldi_slots.w; k.mel_start = ctx->kaldi_slots.start;
   ProfScope ps(ctx, AFE_K_FBANK, s);
-  return afe_launch_fbank_pipe(k, ctx->num_sms, s);
+  return afe_launch(k, FbankKernel<T>::S::kBytes, ctx->num_sms * FbankKernel<T>::kMinBlocks, s);
 }
 
 }  // namespace
@@ -107,7 +107,7 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
   // into one block is normalised by that block right after its last tile (its raw rows are still
   // in L2); the others -- at most one per block boundary -- and those without frames go to the
   // stats / norm kernels.
-  const long grid = afe_async_grid(l.ntiles, ctx->num_sms);
+  const long grid = afe_async_grid(l.ntiles, ctx->num_sms * FbankKernel<double>::kMinBlocks);
   const long per = grid > 0 ? (l.ntiles + grid - 1) / grid : 1;
   int nsel = 0;
   int64_t acc = 0, rows = 0, tp_max = 0;
