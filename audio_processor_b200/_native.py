@@ -23,6 +23,8 @@ AFE_ERR_UNSUPPORTED = -4
 PRECISION_F64 = 0
 PRECISION_F32 = 1
 FBANK_RAW = 1
+FBANK_STATIC_SCRATCH_BYTES = 8 << 20
+FBANK_STATIC_MAX_BATCH = 256
 K_COUNT = 9
 
 c_i64p = C.POINTER(C.c_int64)
@@ -86,6 +88,8 @@ SIGNATURES = {
     "afe_fbank_workspace_bytes": (C.c_size_t, [c_i64p, C.c_int]),
     "afe_fbank_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
                                   C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "afe_fbank_batch_static": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,
+                                         C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "afe_fbank_batch_placed": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, c_i64p, c_i64p,
                                          C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "afe_acoustic_batch_placed": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), c_i64p, C.c_int, C.c_int,

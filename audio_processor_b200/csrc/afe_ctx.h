@@ -54,6 +54,7 @@ struct afe_ctx {
   std::map<std::pair<int, int>, afe::DeviceTaps> taps;          // (orig, new) -> bank
   std::vector<afe::StagingBlock> staging;
   std::vector<void*> owned;                                     // device allocations to free
+  void* fbank_static_scratch = nullptr;                         // device address of afe_fbank.cu's static scratch array
   // optional per-kernel timing (afe_profile_*): (kernel id, start event, stop event)
   bool profiling = false;
   struct ProfRec { int id; void* e0; void* e1; };
@@ -76,6 +77,7 @@ struct afe_ctx {
 };
 
 namespace afe {
+int fbank_static_setup(afe_ctx* ctx);            // afe_fbank.cu: cudaGetSymbolAddress of the static scratch (device current)
 // brackets one kernel launch with events when profiling is on; always counts the launch
 struct ProfScope {
   afe_ctx* c; int id; cudaStream_t s; void* e1 = nullptr;

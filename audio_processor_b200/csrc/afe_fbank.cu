@@ -85,16 +85,17 @@ namespace {
 // shared body: utterance b lands at frame row rows_of[b] of d_features, padded to tp_of[b] frames
 int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
               const int64_t* rows_of, const int64_t* tp_of, float padding_value, int precision, int flags,
-              float* d_features, int32_t* d_mask, void* d_workspace, size_t workspace_bytes, const char* who) {
+              float* d_features, int32_t* d_mask, void* d_workspace, size_t workspace_bytes, const char* who,
+              unsigned char* h_desc = nullptr /* caller-owned host block for the descriptors instead of the pinned pool */) {
   const bool raw_only = (flags & AFE_FBANK_RAW) != 0;
   const FbankLayout l = fbank_layout(h_lengths, batch);
   if (workspace_bytes < l.total) return fail(AFE_ERR_WORKSPACE, std::string(who) + ": workspace too small");
   cudaStream_t s = (cudaStream_t)stream;
 
   // descriptors: pinned staging -> head of the workspace
-  StagingBlock* blk = ctx->staging_acquire(l.desc_bytes);
-  if (!blk) return AFE_ERR_CUDA;
-  unsigned char* h = static_cast<unsigned char*>(blk->host);
+  StagingBlock* blk = h_desc ? nullptr : ctx->staging_acquire(l.desc_bytes);
+  if (!h_desc && !blk) return AFE_ERR_CUDA;
+  unsigned char* h = h_desc ? h_desc : static_cast<unsigned char*>(blk->host);
   const float** hw = reinterpret_cast<const float**>(h + l.off_wave);
   int64_t* hl = reinterpret_cast<int64_t*>(h + l.off_len);
   int64_t* hp = reinterpret_cast<int64_t*>(h + l.off_prefix);
@@ -127,12 +128,12 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
   }
   hp[batch] = acc;
   if (bad || (rows > 0 && (!d_features || (!raw_only && !d_mask)))) {
-    ctx->staging_submit(blk, s);
+    if (blk) ctx->staging_submit(blk, s);
     return fail(AFE_ERR_INVALID, std::string(who) + ": NULL waveform / output or inconsistent placement");
   }
   unsigned char* ws = static_cast<unsigned char*>(d_workspace);
   const int up = dev_upload_async(ws, h, l.desc_bytes, s);
-  ctx->staging_submit(blk, s);
+  if (blk) ctx->staging_submit(blk, s);
   if (up != 0) return AFE_ERR_CUDA;
 
   BatchDesc d;
@@ -203,6 +204,73 @@ int afe_fbank_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_wav
     return fail(AFE_ERR_INVALID, "afe_fbank_batch_placed: unknown precision");
   return fbank_run(ctx, stream, h_waves, h_lengths, batch, h_out_rows, h_padded_frames, padding_value, precision,
                    flags, d_features, d_mask, d_workspace, workspace_bytes, "afe_fbank_batch_placed");
+}
+
+}  // extern "C"
+
+// ---- afe_fbank_batch_static: the same featuriser for callers that must not allocate ----------------------
+// (no counterpart in the reference, see include/afe.h)
+// The workspace (descriptors | tile partials | utterance statistics) is a file-scope device array that every
+// GPU loading the library holds until exit.  Its name is only a host-side stand-in in host code: the device
+// address is taken once per device with cudaGetSymbolAddress at set-up (afe_create, that device current) and
+// kept in the context.  Device code never names the array; nothing in it has to start at zero (every byte a
+// kernel reads was written earlier in the same call), and calls that overlap on the GPU race on it.
+namespace {
+constexpr size_t kStaticScratchBytes = (size_t)AFE_FBANK_STATIC_SCRATCH_BYTES;
+#if AFE_CUDA
+static __device__ __align__(256) unsigned char g_fbank_static_scratch[kStaticScratchBytes];
+#else
+alignas(256) static unsigned char g_fbank_static_scratch[kStaticScratchBytes];
+#endif
+}  // namespace
+
+namespace afe {
+int fbank_static_setup(afe_ctx* ctx) {
+#if AFE_CUDA
+  void* p = nullptr;
+  const cudaError_t e = cudaGetSymbolAddress(&p, g_fbank_static_scratch);
+  if (e != cudaSuccess || !p) { note_error("cudaGetSymbolAddress(fbank static scratch)", cudaGetErrorString(e)); return -1; }
+  ctx->fbank_static_scratch = p;
+#else
+  ctx->fbank_static_scratch = g_fbank_static_scratch;
+#endif
+  return 0;
+}
+}  // namespace afe
+
+extern "C" {
+
+int afe_fbank_batch_static(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
+                           int group_size, float padding_value, int precision, int flags, float* d_features,
+                           int32_t* d_mask) {
+  if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch_static: bad arguments");
+  if (batch == 0) return AFE_OK;
+  if (!h_waves || !h_lengths) return fail(AFE_ERR_INVALID, "afe_fbank_batch_static: NULL argument");
+  if (precision != AFE_PRECISION_F64 && precision != AFE_PRECISION_F32)
+    return fail(AFE_ERR_INVALID, "afe_fbank_batch_static: unknown precision");
+  if (batch > AFE_FBANK_STATIC_MAX_BATCH)
+    return fail(AFE_ERR_WORKSPACE, "afe_fbank_batch_static: batch of " + std::to_string(batch) + " waveforms exceeds the maximum of " +
+                                       std::to_string(AFE_FBANK_STATIC_MAX_BATCH) + "; use afe_fbank_batch with a caller workspace");
+  const FbankLayout l = fbank_layout(h_lengths, batch);
+  if (l.total > kStaticScratchBytes)
+    return fail(AFE_ERR_WORKSPACE, "afe_fbank_batch_static: the batch needs " + std::to_string(l.total) + " bytes of scratch, the static array holds " +
+                                       std::to_string(kStaticScratchBytes) + " (about " + std::to_string(kStaticScratchBytes / (2 * kMel * sizeof(double)) * kFbTile / 100) +
+                                       " s of audio per call); use afe_fbank_batch with a caller workspace");
+  if (!ctx->fbank_static_scratch) return fail(AFE_ERR_CUDA, "afe_fbank_batch_static: the static scratch was not set up for this device");
+  // descriptors and placement on the stack: no pinned pool, no heap block whose size depends on the call
+  alignas(16) unsigned char h_desc[16 * 1024];
+  static_assert(sizeof(h_desc) >= (size_t)AFE_FBANK_STATIC_MAX_BATCH * 56 + 16 * 9, "descriptor block of the largest batch");
+  if (l.desc_bytes > sizeof(h_desc)) return fail(AFE_ERR_WORKSPACE, "afe_fbank_batch_static: descriptor block too large");
+  int64_t rows_of[AFE_FBANK_STATIC_MAX_BATCH], tp_of[AFE_FBANK_STATIC_MAX_BATCH];
+  const int G = group_size > 0 ? group_size : batch;
+  int64_t rows = 0;
+  for (int g0 = 0; g0 < batch; g0 += G) {
+    const int n = std::min(G, batch - g0);
+    const int64_t tp = afe_fbank_padded_frames(h_lengths + g0, n);
+    for (int b = g0; b < g0 + n; ++b) { rows_of[b] = rows; tp_of[b] = tp; rows += tp; }
+  }
+  return fbank_run(ctx, stream, h_waves, h_lengths, batch, rows_of, tp_of, padding_value, precision, flags, d_features,
+                   d_mask, ctx->fbank_static_scratch, kStaticScratchBytes, "afe_fbank_batch_static", h_desc);
 }
 
 }  // extern "C"

@@ -224,7 +224,7 @@ int afe_create(int device, afe_ctx** out) {
   int sms = 0;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0) c->num_sms = sms;
 #endif
-  bool ok = true;
+  bool ok = fbank_static_setup(c) == 0;
   {
     // window tables are role-major for the FFT's stage 1: t[role][n1] = w[16 n1 + role] (afe_rfft512.h)
     std::vector<double> w = make_povey_window();

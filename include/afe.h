@@ -178,6 +178,22 @@ int afe_fbank_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_wav
                            float padding_value, int precision, int flags, float* d_features, int32_t* d_mask,
                            void* d_workspace, size_t workspace_bytes);
 
+/* afe_fbank_batch for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as afe_fbank_batch minus the workspace: the scratch (descriptors,
+ * tile partials, utterance statistics) is a static device array of AFE_FBANK_STATIC_SCRATCH_BYTES inside the
+ * library (every GPU that loads the library holds it until exit), its device address taken once per device in
+ * afe_create.  The call performs no cudaMalloc / cudaFree / pinned or event allocation (keep afe_profile_enable
+ * off: profiling creates events).  Limits: batch <= AFE_FBANK_STATIC_MAX_BATCH and
+ * afe_fbank_workspace_bytes(h_lengths, batch) <= AFE_FBANK_STATIC_SCRATCH_BYTES (about 80 full 25 s chunks);
+ * beyond either it returns AFE_ERR_WORKSPACE with a message naming the limit.  All calls on a device share the one
+ * array: calls that overlap on the GPU (two streams, two threads) race on it -- serialise them on one stream. */
+#define AFE_FBANK_STATIC_SCRATCH_BYTES (8u << 20)
+#define AFE_FBANK_STATIC_MAX_BATCH 256
+int afe_fbank_batch_static(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
+                           int batch, int group_size, float padding_value, int precision, int flags,
+                           float* d_features, int32_t* d_mask);
+
 /* AcousticSentimentAnalyzer._extract_acoustic_features for a batch of mono 16 kHz
  * waveforms (services/sentiment_analysis.py:807-894).  d_out is (batch, 38) float32 in
  * the reference's key order, with slot 11 ("tempo") holding the spectral-flux energy
