@@ -131,28 +131,20 @@ class AudioProcessor:
             else:
                 waveform = fe.resample(waveform, sample_rate, self.target_sample_rate)
             sample_rate = self.target_sample_rate
-        chunk_samples = int(self.chunk_duration_sec * sample_rate)
-        overlap_samples = int(self.overlap_sec * sample_rate)
-        step_samples = chunk_samples - overlap_samples
-        total_samples = waveform.shape[1]
+        # integer contract of the reference (:115-118): int() truncation of seconds x rate, step = window - overlap
+        window = int(self.chunk_duration_sec * sample_rate)
+        hop = window - int(self.overlap_sec * sample_rate)
         if waveform.shape[0] == 2:
-            agent_waveform = waveform[0].unsqueeze(0)
-            client_waveform = waveform[1].unsqueeze(0)
-            mixed_waveform = mixed if mixed is not None else fe.mix_stereo(waveform)
+            agent, client = waveform[0:1], waveform[1:2]            # views of the resampled call
+            both = mixed if mixed is not None else fe.mix_stereo(waveform)
         else:
-            agent_waveform = client_waveform = mixed_waveform = waveform
-        chunks: List[Dict[str, Any]] = []
-        for chunk_idx, (start, end) in enumerate(chunk_table(total_samples, chunk_samples, step_samples)):
-            chunks.append({
-                "file_name": f"{file_name}",
-                "stereo_waveform": mixed_waveform[:, start:end],
-                "agent_waveform": agent_waveform[:, start:end],
-                "client_waveform": client_waveform[:, start:end],
-                "chunk_idx": chunk_idx,
-                "start_time": start / sample_rate,
-                "end_time": end / sample_rate,
-            })
-        return chunks, agent_waveform, client_waveform
+            agent = client = both = waveform                          # mono: the three streams alias one tensor
+        name = f"{file_name}"
+        chunks: List[Dict[str, Any]] = [
+            {"file_name": name, "stereo_waveform": both[:, lo:hi], "agent_waveform": agent[:, lo:hi],
+             "client_waveform": client[:, lo:hi], "chunk_idx": n, "start_time": lo / sample_rate, "end_time": hi / sample_rate}
+            for n, (lo, hi) in enumerate(chunk_table(waveform.shape[1], window, hop))]
+        return chunks, agent, client
 
     # -------------------------------------------------------------- reference :170-181
     def bucket_chunks(self, chunks: Sequence[Dict]) -> List[List[Dict]]:
@@ -201,8 +193,8 @@ class AudioProcessor:
         ``processor(...)`` call per slice would) and handed to the model as views -- no numpy hop."""
         if not chunks:
             return []
-        batch_size = int(self.config["batch_size"])
-        results: List[Dict] = []
+        size = int(self.config["batch_size"])
+        done: List[Dict] = []
         if bool(self.config.get("enable_length_bucketing", True)):
             try:
                 chunks = sorted(chunks, key=lambda c: int(c.get("stereo_waveform", c.get("agent_waveform")).shape[1]))
@@ -210,29 +202,27 @@ class AudioProcessor:
                 pass
         ahead_n = max(1, int(self.config.get("featurise_ahead_batches", 64)))
         ahead = None                  # (first chunk, batch size, [features per slice])
-        i = 0
-        while i < len(chunks):
-            batch_end = min(i + batch_size, len(chunks))
-            batch_chunks = chunks[i:batch_end]
+        at = 0
+        while at < len(chunks):
+            stop = min(at + size, len(chunks))
+            members = chunks[at:stop]
             try:
-                if ahead is None or ahead[1] != batch_size or i >= ahead[0] + batch_size * len(ahead[2]):
-                    ahead = (i, batch_size, self._featurise_ahead(chunks[i:i + ahead_n * batch_size], batch_size))
-                features = ahead[2][(i - ahead[0]) // batch_size]
-                results.extend(self._process_single_batch(batch_chunks, features))
+                if ahead is None or ahead[1] != size or at >= ahead[0] + size * len(ahead[2]):
+                    ahead = (at, size, self._featurise_ahead(chunks[at:at + ahead_n * size], size))
+                done.extend(self._process_single_batch(members, ahead[2][(at - ahead[0]) // size]))
                 self._cleanup_memory()
             except Exception as e:
-                self.logger.error(f"Error processing batch {i // batch_size + 1}: {e}")
-                if "out of memory" in str(e).lower() and batch_size > 1:
-                    new_bs = max(1, batch_size // 2)
-                    self.logger.warning(f"CUDA OOM detected. Reducing batch size {batch_size} -> {new_bs} and retrying this slice")
-                    batch_size, ahead = new_bs, None
+                self.logger.error(f"slice {at // size + 1} (chunks {at}..{stop - 1}) failed: {e}")
+                if "out of memory" in str(e).lower() and size > 1:
+                    self.logger.warning(f"device memory exhausted: batch size {size} -> {max(1, size // 2)}, same slice again")
+                    size, ahead = max(1, size // 2), None
                     self._release_cache()
-                    continue                                   # retry the same i with the smaller batch
-                for chunk in batch_chunks:
+                    continue                                   # same `at`, smaller slice
+                for chunk in members:
                     chunk.update({**_EMPTY, "error": str(e)})
-                results.extend(batch_chunks)
-            i = batch_end
-        return results
+                done.extend(members)
+            at = stop
+        return done
 
     def _featurise_ahead(self, chunks: Sequence[Dict], batch_size: int):
         """Features of consecutive slices of ``batch_size`` chunks: a list of ``{"stereo"|"agent"|"client": input_features}``

@@ -26,7 +26,10 @@ struct StagingBlock {
   void* host = nullptr;
   size_t cap = 0;
   void* event = nullptr;                         // cudaEvent_t
-  bool in_flight = false;
+  // kFree -> kReserved (a caller is filling it; its event is still the previous, completed one and must not be
+  // consulted) -> kSubmitted (event recorded after the copy: reusable once the event has completed) -> ...
+  enum State { kFree = 0, kReserved = 1, kSubmitted = 2 };
+  int state = kFree;
 };
 
 }  // namespace afe

@@ -52,13 +52,72 @@ AFE_HD void locate_tile(const BatchDesc& d, long item, int& b, int& t) {
   t = (int)(item - ldg(d.tile_prefix + lo));
 }
 
+// float32 sum of n copies of v exactly as numpy's pairwise add.reduce forms it along contiguous memory
+// (numpy/_core/src/umath/loops_utils.h.src: < 8 sequential; <= 128 eight accumulators, a fixed tree, the
+// remainder sequentially; above that halves rounded down to a multiple of 8).  With equal addends the eight
+// accumulators are equal and their tree is an exact multiplication by 8.  Iterative post-order walk of the
+// halving tree (depth <= 40); only ever called for the constant bins of a silent utterance.
+#if AFE_CUDA
+#define AFE_NOINLINE __noinline__
+#else
+#define AFE_NOINLINE __attribute__((noinline))
+#endif
+AFE_NOINLINE
+#if AFE_CUDA
+__host__ __device__
+#endif
+inline float numpy_pairwise_sum_const(float v, int64_t n) {
+  int64_t size[48];
+  float left[48];
+  signed char state[48];          // 0: descend left, 1: left done -> descend right, 2: both done
+  int sp = 0;
+  size[0] = n; state[0] = 0;
+  float ret = 0.f;
+  while (sp >= 0) {
+    const int64_t m = size[sp];
+    if (m <= 128) {
+      float res;
+      if (m < 8) {
+        res = 0.f;
+        for (int64_t i = 0; i < m; ++i) res += v;
+      } else {
+        float r = v;
+        int64_t i = 8;
+        for (; i < m - (m % 8); i += 8) r += v;
+        res = 8.f * r;
+        for (; i < m; ++i) res += v;
+      }
+      ret = res; --sp;
+      continue;
+    }
+    int64_t n2 = m / 2; n2 -= n2 % 8;
+    if (state[sp] == 0) { state[sp] = 1; size[sp + 1] = n2; state[sp + 1] = 0; ++sp; }
+    else if (state[sp] == 1) { left[sp] = ret; state[sp] = 2; size[sp + 1] = m - n2; state[sp + 1] = 0; ++sp; }
+    else { ret = left[sp] + ret; --sp; }
+  }
+  return ret;
+}
+
 // (mean, 1 / denominator) of one mel bin from its float64 sum and sum of squares over n frames --
 // the reciprocal is formed once per (utterance, bin) so that the normalisation of the utterance's T x 80 values
 // is a subtract and a multiply (within 1.5 ulp of the reference's divide; the contract is 1e-3 absolute) --
-// numpy's mean / var(ddof=1) / sqrt(var + 1e-7) of feature_extraction_seamless_m4t.py:283-288
+// numpy's mean / var(ddof=1) / sqrt(var + 1e-7) of feature_extraction_seamless_m4t.py:257-262.
+// A bin that is constant over the utterance (digital silence: every frame at the log floor) has variance 0 and the
+// reference's output is its OWN float32 rounding noise over sqrt(1e-7): mean32 = pairwise_sum(v, n) / n differs from
+// v by a few ulp, and (v - mean32) / 3.16e-4 reaches 6e-3.  For such bins (float64 variance < 1e-10: the values
+// agree to ~10 ulp) the float32 mean and variance are formed the way numpy forms them, bit for bit.
 AFE_HD void fbank_mean_den(double s, double ss, int n, float& mean_out, float& den_out) {
   const double mean = s / (double)n;
   const double var = (ss - s * mean) / (double)(n - 1);      // ddof = 1; n == 1 -> 0/0 = NaN
+  if (var < 1e-10 && n > 1) {
+    const float v = (float)mean;
+    const float mean32 = (float)((double)numpy_pairwise_sum_const(v, n) / (double)n);
+    const float d = v - mean32;
+    const float var32 = (float)((double)numpy_pairwise_sum_const(d * d, n) / (double)(n - 1));
+    mean_out = mean32;
+    den_out = 1.f / std::sqrt(var32 + 1e-7f);
+    return;
+  }
   const float varf = (float)var;
   mean_out = (float)mean;
   den_out = 1.f / std::sqrt(varf + 1e-7f);

@@ -381,8 +381,9 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
       if (tid == prefetch_thread<K>::value && item + 1 < end) {
         typename K::Item nx = k.next(cur, item + 1);
         nx.buf = buf ^ 1;
-        // no proxy fence: the buffer's last generic-proxy accesses (phase 1 reads, or the phase 0 copy of an
-        // unaligned tile) were performed before the barriers this thread has since passed
+        // the buffer's last generic-proxy accesses (phase 1 reads, or the phase 0 stores of an unaligned tile) were
+        // ordered before this point by the block barriers; the proxy fence orders them before the async-proxy write
+        fence_proxy_async();
         afe_issue_stage(k, nx, afe_smem + K::kStageOff + (size_t)(buf ^ 1) * K::kStageBytes, &bars[buf ^ 1]);
         items[buf ^ 1] = nx;
       }

@@ -84,14 +84,13 @@ using namespace afe;
 afe::StagingBlock* afe_ctx::staging_acquire(size_t bytes) {
   std::lock_guard<std::mutex> lock(mu);
   for (auto& b : staging) {
-    if (b.cap < bytes) continue;
-    if (b.in_flight) {
+    if (b.cap < bytes || b.state == StagingBlock::kReserved) continue;
+    if (b.state == StagingBlock::kSubmitted) {
 #if AFE_CUDA
       if (cudaEventQuery((cudaEvent_t)b.event) != cudaSuccess) continue;
 #endif
-      b.in_flight = false;
     }
-    b.in_flight = true;                           // reserved by this call
+    b.state = StagingBlock::kReserved;            // owned by this call until staging_submit
     return &b;
   }
   if (staging.capacity() < 256) staging.reserve(256);     // keep pointers stable
@@ -105,18 +104,19 @@ afe::StagingBlock* afe_ctx::staging_acquire(size_t bytes) {
   if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { host_pinned_free(nb.host); return nullptr; }
   nb.event = ev;
 #endif
-  nb.in_flight = true;
+  nb.state = StagingBlock::kReserved;
   staging.push_back(nb);
   return &staging.back();
 }
 
 void afe_ctx::staging_submit(afe::StagingBlock* blk, cudaStream_t stream) {
+  std::lock_guard<std::mutex> lock(mu);
 #if AFE_CUDA
   cudaEventRecord((cudaEvent_t)blk->event, stream);
+  blk->state = StagingBlock::kSubmitted;
 #else
   (void)stream;
-  std::lock_guard<std::mutex> lock(mu);
-  blk->in_flight = false;
+  blk->state = StagingBlock::kFree;
 #endif
 }
 

@@ -71,3 +71,41 @@ def test_package_has_no_cpu_fallback(tmp_path):
             if f.endswith(".py"):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+# ---------------------------------------------------------------- host tables through the C ABI (no GPU needed)
+def _golden_tables():
+    import os
+    import numpy as np
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "tables.npz"))
+
+
+def test_c_abi_chunk_table_matches_reference_golden():
+    """afe_chunk_table (the product library, host code) against the reference's split_audio on every golden
+    edge total: 0, 1, 399 999, 400 000, 400 001, 784 000, 784 001, 960 000, 4 800 000."""
+    from audio_processor_b200.audio_processor import chunk_table
+    g = _golden_tables()
+    rows = g["chunk_rows"]
+    assert len(g["chunk_totals"]) == 9
+    for tot in g["chunk_totals"]:
+        exp = rows[rows[:, 0] == tot]
+        got = chunk_table(int(tot), 400_000, 384_000)
+        assert len(got) == len(exp), int(tot)
+        for i, (s, e) in enumerate(got):
+            assert (s, e) == (int(exp[i, 2]), int(exp[i, 3])), (int(tot), i)
+            assert s / 16000 == exp[i, 4] and e / 16000 == exp[i, 5]        # start_time / end_time floats, bit-exact
+
+
+def test_c_abi_segment_table_matches_reference_golden():
+    """afe_segment_table against the reference's _extract_segments: config windows (25 s) and code default (20 s)."""
+    from audio_processor_b200.speech_segment import merge_segments, segment_table
+    g = _golden_tables()
+    iv = [tuple(r) for r in g["seg_intervals"].tolist()]
+    n = int(g["seg_num_samples"][0])
+    for tag, max_len in (("seg_cfg", 25.0), ("seg_default", 20.0)):
+        got = segment_table(n, 16000, iv, 0.5, max_len, 0.5)
+        exp = g[tag]
+        assert len(got) == len(exp), tag
+        for (a, b, st, en), (cnt, est, een) in zip(got, exp):
+            assert b - a == int(cnt) and st == est and en == een, tag
+    assert [list(p) for p in merge_segments([tuple(r) for r in g["merge_in"].tolist()], 0.8)] == g["merge_out"].tolist()

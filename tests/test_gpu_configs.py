@@ -141,24 +141,62 @@ def test_cfg2_full_size_properties_and_spot_parity(fe):
     assert torch.equal(fa, fb)
     assert torch.equal(res.acoustic_rows[0 * 13 + 2], res.acoustic_rows[3 * 13 + 2])
     assert int(res.acoustic_status.sum()) == 0
-    # spot parity against the oracle: one full chunk and the short tail chunk of call 1, agent stream
+    # oracle parity on EVERY chunk of one call: 13 chunks x 3 streams (fbank) and both speakers (acoustic)
     ref = np_resample.resample(calls[1].numpy(), sr, 16000)
     assert np.array_equal(res.waveforms[1][0].cpu().numpy(), ref)
-    for chunk_idx in (4, 12):
+    ref_mixed = (ref[0] + ref[1]) * np.float32(0.5)
+    assert np.array_equal(res.waveforms[1][1].cpu().numpy()[0], ref_mixed)
+    streams = {"stereo": ref_mixed, "agent": ref[0], "client": ref[1]}
+    from audio_processor_b200.acoustic import TEMPO_SLOT, _tempo
+    worst = 0.0
+    for chunk_idx in range(13):
         j = 1 * 13 + chunk_idx
         pos = res.order.index(j)
-        feat, mask = res.features["agent"][pos // 16]
         s, e = res.chunks[j][2], res.chunks[j][3]
         T = 1 + (e - s - 400) // 160
-        Tp = feat.shape[1] * 2
-        ref_f, _ = np_fbank.featurise([ref[0, s:e]])
-        got = feat[pos % 16].reshape(Tp, 80)[:T - (T % 2)].cpu().numpy()
-        assert np.max(np.abs(got - ref_f.reshape(-1, 80)[:T - (T % 2)])) <= 1e-3
-        ref_a = np_acoustic.acoustic_features(ref[0, s:e])
-        vals = res.acoustic_rows[j].tolist()
+        for key, wave in streams.items():
+            feat, mask = res.features[key][pos // 16]
+            Tp = feat.shape[1] * 2
+            ref_f, _ = np_fbank.featurise([wave[s:e]])
+            got = feat[pos % 16].reshape(Tp, 80)[:T - (T % 2)].cpu().numpy()
+            err = float(np.max(np.abs(got - ref_f.reshape(-1, 80)[:T - (T % 2)])))
+            worst = max(worst, err)
+            assert err <= 1e-3, (chunk_idx, key, err)
+            assert int(mask[pos % 16].sum()) == T // 2
+        for speaker, wave in ((0, ref[0]), (1, ref[1])):
+            ref_a = np_acoustic.acoustic_features(wave[s:e])
+            vals = res.acoustic_rows[speaker * n + j].tolist()
+            vals[TEMPO_SLOT] = _tempo(vals[TEMPO_SLOT], e - s, 16000)
+            _acoustic_close(vals, list(ref_a.values()))
+    print(f"cfg2 call 1: 39 chunk-streams, worst fbank error {worst:.2e}")
+
+
+def test_cfg5_full_chunk_at_the_hour_offset(fe):
+    """cfg5's 1-hour call has 150 chunks; chunk 149 starts 57 216 000 samples in.  A waveform of that length is
+    built on the device, chunk 148 (full) and 149 (the 384 000-sample tail) are featurised through split_audio's
+    views at their true offsets (beyond 2^25 samples) and checked against the oracle: fbank, mask and the 38
+    acoustic features."""
+    import torch
+    from audio_processor_b200 import AudioProcessor
+    n = 57_600_000
+    g = torch.Generator(device=fe.device).manual_seed(15)
+    y = (torch.rand(n, generator=g, device=fe.device) - 0.5).unsqueeze(0)
+    ap = AudioProcessor({"chunk_duration_sec": 25, "overlap_sec": 1, "target_sample_rate": 16000, "batch_size": 16, "gpu_index": 0})
+    chunks, agent, client = ap.split_audio(y, 16000, "hour.wav")
+    assert len(chunks) == 150 and agent.data_ptr() == client.data_ptr() == y.data_ptr()
+    assert (chunks[149]["start_time"], chunks[149]["end_time"]) == (3576.0, 3600.0)
+    for idx in (148, 149):
+        w = chunks[idx]["agent_waveform"]
+        assert w.data_ptr() == y.data_ptr() + 4 * 384_000 * idx
+        feat, mask = fe.fbank([w[0]])
+        ref_f, ref_m = np_fbank.featurise([w[0].cpu().numpy()])
+        assert np.array_equal(mask.cpu().numpy(), ref_m)
+        _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+        a, st = fe.acoustic([w[0]])
         from audio_processor_b200.acoustic import TEMPO_SLOT, _tempo
-        vals[TEMPO_SLOT] = _tempo(vals[TEMPO_SLOT], e - s, 16000)
-        _acoustic_close(vals, list(ref_a.values()))
+        vals = a[0].tolist()
+        vals[TEMPO_SLOT] = _tempo(vals[TEMPO_SLOT], w.shape[1], 16000)
+        _acoustic_close(vals, list(np_acoustic.acoustic_features(w[0].cpu().numpy()).values()))
 
 
 # ------------------------------------------------------------------ threading contract (SURVEY 8b)
