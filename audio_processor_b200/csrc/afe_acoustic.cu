@@ -58,6 +58,7 @@ size_t afe_acoustic_workspace_bytes(const int64_t* h_lengths, int batch) {
 
 int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
                        int sample_rate, float* d_out, int32_t* d_status, void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_acoustic_batch");
   return afe_acoustic_batch_placed(ctx, stream, h_waves, h_lengths, batch, sample_rate, nullptr, d_out, d_status,
                                    d_workspace, workspace_bytes);
 }
@@ -65,6 +66,7 @@ int afe_acoustic_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, 
 int afe_acoustic_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths,
                               int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
                               int32_t* d_status, void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_acoustic_batch_placed");
   return afe_acoustic_batch_scaled(ctx, stream, h_waves, h_lengths, batch, sample_rate, h_out_index, d_out, d_status,
                                    nullptr, nullptr, 0, nullptr, d_workspace, workspace_bytes);
 }
@@ -73,6 +75,7 @@ int afe_acoustic_batch_scaled(afe_ctx* ctx, void* stream, const float* const* h_
                               int batch, int sample_rate, const int32_t* h_out_index, float* d_out,
                               int32_t* d_status, const double* d_mean, const double* d_scale, int n_features,
                               double* d_scaled, void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_acoustic_batch_scaled");
   if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_acoustic_batch: bad arguments");
   if (d_scaled && (!d_mean || !d_scale || n_features <= 0))
     return fail(AFE_ERR_INVALID, "afe_acoustic_batch_scaled: scaler mean / scale / n_features missing");

@@ -175,6 +175,7 @@ extern "C" {
 int afe_fbank_batch(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
                     int group_size, float padding_value, int precision, int flags, float* d_features,
                     int32_t* d_mask, void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_fbank_batch");
   if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch: bad arguments");
   if (batch == 0) return AFE_OK;
   if (!h_waves || !h_lengths || !d_workspace) return fail(AFE_ERR_INVALID, "afe_fbank_batch: NULL argument");
@@ -196,6 +197,7 @@ int afe_fbank_batch_placed(afe_ctx* ctx, void* stream, const float* const* h_wav
                            int batch, const int64_t* h_out_rows, const int64_t* h_padded_frames,
                            float padding_value, int precision, int flags, float* d_features, int32_t* d_mask,
                            void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_fbank_batch_placed");
   if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch_placed: bad arguments");
   if (batch == 0) return AFE_OK;
   if (!h_waves || !h_lengths || !h_out_rows || !h_padded_frames || !d_workspace)
@@ -243,6 +245,7 @@ extern "C" {
 int afe_fbank_batch_static(afe_ctx* ctx, void* stream, const float* const* h_waves, const int64_t* h_lengths, int batch,
                            int group_size, float padding_value, int precision, int flags, float* d_features,
                            int32_t* d_mask) {
+  AFE_NVTX("afe_fbank_batch_static");
   if (!ctx || batch < 0) return fail(AFE_ERR_INVALID, "afe_fbank_batch_static: bad arguments");
   if (batch == 0) return AFE_OK;
   if (!h_waves || !h_lengths) return fail(AFE_ERR_INVALID, "afe_fbank_batch_static: NULL argument");

@@ -270,6 +270,23 @@ struct PlainItem { long item; int buf; int bulk; };
 template <typename T> AFE_HD T tmin(T a, T b) { return a < b ? a : b; }
 template <typename T> AFE_HD T tmax(T a, T b) { return a > b ? a : b; }
 
+// ---------------------------------------------------------------- NVTX range of a C-ABI entry point
+// (the reference has loguru lines only; a timeline tool shows these ranges around the launches)
+#if AFE_CUDA
+}  // namespace afe
+#include <nvtx3/nvToolsExt.h>
+namespace afe {
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#else
+struct NvtxRange { explicit NvtxRange(const char*) {} };
+#endif
+#define AFE_NVTX(name) ::afe::NvtxRange afe_nvtx_range_(name)
+
 // ---------------------------------------------------------------- memory + launch plumbing
 int  dev_set(int device);                         // cudaSetDevice (no-op in emulation)
 void* dev_alloc(size_t bytes);                    // nullptr on failure

@@ -110,6 +110,7 @@ int launch_up2x(afe_ctx* ctx, cudaStream_t s, const ResampleTaps& t, const UpCal
 extern "C" {
 
 int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length, float* d_mixed) {
+  AFE_NVTX("afe_mix_stereo");
   if (!ctx || !d_in || !d_mixed || length < 0) return fail(AFE_ERR_INVALID, "afe_mix_stereo: bad arguments");
   MixKernel k{d_in, d_mixed, length};
   ProfScope ps(ctx, AFE_K_MIX, (cudaStream_t)stream);
@@ -119,6 +120,7 @@ int afe_mix_stereo(afe_ctx* ctx, void* stream, const float* d_in, int64_t length
 
 int afe_resample(afe_ctx* ctx, void* stream, const float* d_in, int rows, int64_t length, int orig_hz,
                  int new_hz, float* d_out, float* d_mixed, int64_t out_length) {
+  AFE_NVTX("afe_resample");
   if (!ctx || !d_in || !d_out || rows <= 0 || length < 0 || orig_hz <= 0 || new_hz <= 0)
     return fail(AFE_ERR_INVALID, "afe_resample: bad arguments");
   if (orig_hz == new_hz) return fail(AFE_ERR_INVALID, "afe_resample: equal rates need no resampling");
@@ -165,6 +167,7 @@ size_t afe_resample_batch_workspace_bytes(int ncalls) {
 }
 
 int afe_pcm16_to_float(afe_ctx* ctx, void* stream, const int16_t* d_in, int64_t count, float* d_out) {
+  AFE_NVTX("afe_pcm16_to_float");
   if (!ctx || count < 0 || (count > 0 && (!d_in || !d_out))) return fail(AFE_ERR_INVALID, "afe_pcm16_to_float: bad arguments");
   if (count == 0) return AFE_OK;
   Pcm16Kernel k{d_in, d_out, count};
@@ -180,6 +183,7 @@ static int resample_batch_impl(afe_ctx* ctx, void* stream, const void* const* h_
 int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, const int64_t* h_lengths, int ncalls,
                        int rows, int orig_hz, int new_hz, float* const* h_out, float* const* h_mixed,
                        void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_resample_batch");
   return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), 0, h_lengths, ncalls, rows,
                              orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
 }
@@ -187,6 +191,7 @@ int afe_resample_batch(afe_ctx* ctx, void* stream, const float* const* h_in, con
 int afe_resample_batch_pcm16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
                              int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
                              float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_resample_batch_pcm16");
   return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), 1, h_lengths, ncalls, rows,
                              orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
 }
@@ -194,12 +199,14 @@ int afe_resample_batch_pcm16(afe_ctx* ctx, void* stream, const int16_t* const* h
 int afe_resample_batch_wav16(afe_ctx* ctx, void* stream, const int16_t* const* h_in, const int64_t* h_lengths,
                              int ncalls, int rows, int orig_hz, int new_hz, float* const* h_out,
                              float* const* h_mixed, void* d_workspace, size_t workspace_bytes) {
+  AFE_NVTX("afe_resample_batch_wav16");
   return resample_batch_impl(ctx, stream, reinterpret_cast<const void* const*>(h_in), 2, h_lengths, ncalls, rows,
                              orig_hz, new_hz, h_out, h_mixed, d_workspace, workspace_bytes);
 }
 
 int afe_wav_decode(afe_ctx* ctx, void* stream, const void* d_frames, int format, int channels, int64_t num_frames,
                    float* d_out) {
+  AFE_NVTX("afe_wav_decode");
   if (!ctx || channels <= 0 || num_frames < 0 || format < AFE_WAV_U8 || format > AFE_WAV_F64 ||
       (num_frames > 0 && (!d_frames || !d_out)))
     return fail(AFE_ERR_INVALID, "afe_wav_decode: bad arguments");

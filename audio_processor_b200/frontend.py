@@ -265,7 +265,8 @@ class CallFrontend:
         """Chunk table of every call (split_audio, audio_processor.py:115-160), the stable length sort of
         transcribe_batch (:170-181), the padded length of each batch of ``batch_size`` chunks and the
         output row of every chunk.  Cached: batches of equally long calls repeat."""
-        key = (lengths, sample_rate)
+        # every attribute the layout depends on is part of the key: they are public and may be changed between calls
+        key = (lengths, sample_rate, self.chunk_duration_sec, self.overlap_sec, self.target_sample_rate, self.batch_size)
         plan = self._plans.get(key)
         if plan is not None:
             return plan
@@ -292,6 +293,11 @@ class CallFrontend:
             self._plans.pop(next(iter(self._plans)))
         self._plans[key] = plan
         return plan
+
+    def clear_plans(self) -> None:
+        """Forget the cached layouts (bench.py: the end-to-end steps pay the planning, as ragged batches would)."""
+        self._plans.clear()
+        self._tables.clear()
 
     def _chunk_table(self, total: int, chunk: int, step: int):
         key = (total, chunk, step)

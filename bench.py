@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument("--impl", default="afe", choices=["afe", "reference"])
     ap.add_argument("--calls", type=int, default=64, help="calls per GPU per step")
     ap.add_argument("--call-seconds", type=float, default=300.0)
-    ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic calls generated (cycled)")
+    ap.add_argument("--distinct", type=int, default=0, help="distinct synthetic calls per GPU (0: as many as --calls, no reuse)")
     ap.add_argument("--precision", default="f64", choices=["f64", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sub-batch", type=int, default=0, help="calls per pipelined sub-batch (0: library default)")
@@ -106,28 +106,42 @@ def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
+CPU_GROUP_CALLS = 16          # calls a CPU worker buckets together: the reference's length sort needs >= batch_size calls
+
+
+def cpu_sample_config(a):
+    """The bounded CPU sample of the cfg2 workload: every worker process runs one file batch of 16 calls of
+    --call-seconds, chunks pooled and bucketed in batches of 16 like audio_processor.py:170-181."""
+    cores = os.cpu_count() or 1
+    return max(1, min(cores, 64)), CPU_GROUP_CALLS, a.call_seconds
+
+
 def run_reference(a):
-    """The reference's CPU implementation of the path (oracle/libref: same torchaudio /
-    transformers / torch calls) on the host cores, bounded sample per step."""
+    """The reference's CPU implementation of the path (oracle/libref: same torchaudio / transformers / torch calls)
+    on all host cores, on the afe arm's workload shape; each step is a bounded sample of it."""
     rank, _, world = dist_env()
     if rank != 0:
         return
     from oracle import libref
-    cores = os.cpu_count() or 1
-    workers = max(1, min(cores, 64))
-    vals, walls = [], []
-    desc = ""
-    for i in range(a.warmup + a.steps):
-        v, wall, desc = libref.timed_sample(workers, calls_per_worker=3, seconds=60.0)
-        if i >= a.warmup:
-            vals.append(v); walls.append(wall)
-        if sum(walls) > 240:
-            break
+    workers, group, seconds = cpu_sample_config(a)
+    pool = libref.worker_pool(workers)
+    vals, spans, desc = [], [], ""
+    try:
+        for _ in range(a.warmup):                  # warm-up steps: the same path on one short call per worker
+            libref.timed_sample(workers, calls_per_worker=1, seconds=20.0, grouped=True, pool=pool)
+        for _ in range(a.steps):
+            v, span, desc = libref.timed_sample(workers, calls_per_worker=group, seconds=seconds, grouped=True, pool=pool)
+            vals.append(v); spans.append(span)
+            if sum(spans) > 150:                   # keep the whole run within a few minutes
+                break
+    finally:
+        pool.terminate()
     value = sum(vals) / len(vals)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
-            "steps": len(vals), "warmup": a.warmup, "ms_per_step": 1e3 * sum(walls) / len(walls),
+            "steps": len(vals), "warmup": a.warmup, "ms_per_step": 1e3 * sum(spans) / len(spans),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "sample": desc},
+            "config": {"workload": workload_name(a), "calls_per_gpu": a.calls, "call_seconds": a.call_seconds,
+                       "sample": desc, "steps_note": f"{len(vals)} of the requested {a.steps} steps: the run is capped at ~150 s of CPU work"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port", "sample": desc},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -159,13 +173,25 @@ def a_precision_is_f32():
     return _PRECISION[0] == "f32"
 
 
-def ncu_traffic():
-    """Per-launch DRAM bytes of the fbank kernel from the committed ncu summary, if any."""
+def ncu_cfg2_summary():
+    """Key figures of ONE fbank launch of this very step (cfg2), from the committed `ncu --set full` capture
+    (tools/gpu_ncu_bench.sh -> profiles/r02_fbank_cfg2_ncu_summary.json): DRAM bytes and shared-memory wavefronts."""
     try:
-        with open(os.path.join(ROOT, "profiles", "fbank_ncu_summary.json")) as f:
-            return json.load(f).get("dram_bytes_per_frame")
+        with open(os.path.join(ROOT, "profiles", "r02_fbank_cfg2_ncu_summary.json")) as f:
+            return json.load(f)
     except Exception:
+        return {}
+
+
+def smem_roof(frames_per_launch, launch_ms, num_sms, sm_mhz, wavefronts_per_frame):
+    """The kernel's time against its shared-memory floor: wavefronts per frame (ncu, l1tex__data_pipe_lsu_wavefronts_
+    mem_shared) at one wavefront per clock per SM."""
+    if not launch_ms or not sm_mhz or not wavefronts_per_frame:
         return None
+    floor = num_sms * sm_mhz * 1e6 / wavefronts_per_frame
+    got = frames_per_launch / (launch_ms * 1e-3)
+    return {"bound": "shared-memory wavefronts", "wavefronts_per_frame": wavefronts_per_frame, "wavefronts_per_clk_per_sm": 1.0,
+            "floor_frames_per_s": floor, "achieved_frames_per_s": got, "frac": got / floor}
 
 
 def run_afe(a):
@@ -191,7 +217,7 @@ def run_afe(a):
         torch.cuda.synchronize(dev)
 
     # synthetic calls: `distinct` seeded calls per rank, cycled; host copies pinned
-    m = max(1, min(a.distinct, a.calls))
+    m = max(1, min(a.distinct if a.distinct > 0 else a.calls, a.calls))
     pool = [synth.make_call(a.call_seconds, 8000, 100 + rank * 1000 + i, 2).pin_memory() for i in range(m)]
     host_calls = [pool[i % m] for i in range(a.calls)]
     dev_pool = [c.to(dev) for c in pool]
@@ -248,12 +274,30 @@ def run_afe(a):
     f0.record()
     checksum = 0.0
     for _ in range(a.steps):
+        cf.clear_plans()                                      # the host plans the layout every step, as for ragged batches
         r = cf.process_calls(host_calls, 8000, acoustic_to_host=True, sub_batch=sb)
         checksum += float(r.acoustic_rows[:, 0].sum())        # the step's host-side result is consumed
         del r
     f1.record()
     barrier()
     ms_e2e = max(f0.elapsed_time(f1), 1e3 * (time.perf_counter() - t0))
+
+    # ---- the floor under region B: the same pinned buffers, upload only (one cudaMemcpyAsync per call on one
+    # stream, all ranks at once, so GPUs that share a host uplink show it) ---------------------------------
+    sink = [torch.empty_like(c, device=dev) for c in pool]
+    h2d_ms = []
+    for rep_i in range(4):
+        barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        h0.record()
+        for i in range(a.calls):
+            sink[i % m].copy_(host_calls[i], non_blocking=True)
+        h1.record()
+        barrier()
+        if rep_i:
+            h2d_ms.append(h0.elapsed_time(h1))
+    ms_h2d = min(h2d_ms)
+    del sink
 
     # ---- timed region C: end to end from pinned 16-bit wav file images ---------
     # each call is the image of a 16-bit stereo wav file in pinned memory (44-byte RIFF header + interleaved
@@ -271,6 +315,7 @@ def run_afe(a):
     g0.record()
     checksum_pcm = 0.0
     for _ in range(a.steps):
+        cf.clear_plans()
         pcm_calls = [wav.load_pcm16(f)[0] for f in wav_files]
         r = cf.process_calls(pcm_calls, 8000, acoustic_to_host=True, sub_batch=sb)
         checksum_pcm += float(r.acoustic_rows[:, 0].sum())
@@ -279,10 +324,10 @@ def run_afe(a):
     barrier()
     ms_pcm = max(g0.elapsed_time(g1), 1e3 * (time.perf_counter() - t0))
 
-    times = torch.tensor([ms_dev, ms_e2e, ms_pcm], dtype=torch.float64, device=dev)
+    times = torch.tensor([ms_dev, ms_e2e, ms_pcm, ms_h2d], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms_dev, ms_e2e, ms_pcm = float(times[0]), float(times[1]), float(times[2])
+    ms_dev, ms_e2e, ms_pcm, ms_h2d = float(times[0]), float(times[1]), float(times[2]), float(times[3])
 
     if rank == 0:
         total_hours = audio_hours_per_step * a.steps * world
@@ -293,34 +338,51 @@ def run_afe(a):
         # the three streams' frames of a step, spread over however many launches the step used
         frames_per_launch = 3.0 * frames_per_stream * a.steps / max(fb_n, 1)
         achieved = frames_per_launch * FBANK_BYTES_PER_FRAME / (fb_ms / max(fb_n, 1) * 1e-3) / 1e9 if fb_ms > 0 else None
-        traffic_pf = ncu_traffic()
+        ncu = ncu_cfg2_summary()
+        traffic_pf = ncu.get("dram_bytes_per_frame")
         kernel_ms = {k: round(v[0] / a.steps, 4) for k, v in prof.items() if v[1]}
         # the other kernels against the same HBM roof (algorithmic bytes of SURVEY.md 8d per step and GPU):
         # resample 8 kHz stereo 256 000 B per call-second; acoustic tile 640 B per 10 ms frame of each speaker;
         # MFCC pass: the 128 mel-dB floats of every frame, written by the tile kernel and read back once
-        step_bytes = {"resample": 256000.0 * a.calls * a.call_seconds,
-                      "acoustic_tile": 2.0 * stft_frames * (640.0 + 512.0),
-                      "acoustic_mfcc": 2.0 * stft_frames * 512.0}
+        # acoustic: 640 B per 10 ms frame of each speaker + 152 B per waveform -- the 128 mel-dB floats the
+        # tile kernel writes and the MFCC kernel reads back (1 024 B per frame) are an intermediate: overhead, not credit
+        acoustic_bytes = 2.0 * stft_frames * 640.0 + 2.0 * n_chunks * 152.0
+        step_bytes = {"resample": 256000.0 * a.calls * a.call_seconds, "acoustic_tile": acoustic_bytes}
         other = {}
         for k, nbytes in step_bytes.items():
             if k in prof and prof[k][0] > 0:
                 gbps = nbytes / (prof[k][0] / a.steps * 1e-3) / 1e9
                 other[k] = {"achieved": round(gbps, 1), "frac": round(gbps / peak, 4), "unit": "GB/s",
                             "algorithmic_bytes_per_step": nbytes}
+        chain_ms = sum(prof[k][0] for k in ("acoustic_tile", "acoustic_max", "acoustic_mfcc", "acoustic_final") if k in prof) / a.steps
+        if chain_ms > 0:
+            gbps = acoustic_bytes / (chain_ms * 1e-3) / 1e9
+            other["acoustic_chain"] = {"achieved": round(gbps, 1), "frac": round(gbps / peak, 4), "unit": "GB/s",
+                                       "algorithmic_bytes_per_step": acoustic_bytes, "ms_per_step": round(chain_ms, 4),
+                                       "overhead_bytes_per_step": 2.0 * stft_frames * 1024.0,
+                                       "overhead_note": "mel-dB rows written by the tile kernel and read back by the MFCC kernel "
+                                                        "(the global top_db maximum forces the second pass)"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if a.precision == "f64" else "f32", "data": "synthetic",
             "config": {"workload": workload_name(a), "calls_per_gpu": a.calls, "call_seconds": a.call_seconds,
                        "chunks_per_step_per_gpu": n_chunks, "distinct_calls": m, "parallelism": f"dp{world} by file",
-                       "l2": "inputs (1.2 GB/step) larger than L2; no flush needed",
+                       "l2": f"{m} distinct calls per GPU = {m * 2 * a.call_seconds * 8000 * 4 / 1e6:.0f} MB of distinct input per step "
+                             f"({'larger than' if m * 2 * a.call_seconds * 8000 * 4 > 126e6 * 2 else 'NOT larger than twice'} the 126 MB L2); "
+                             "every kernel's input was written by the previous kernel or step, no explicit flush",
                        "fbank_precision": a.precision, "kernel_ms_per_step": kernel_ms,
                        "kernel_ms_note": "per-kernel CUDA-event times from a second pass of the same steps with the acoustic chain "
                                          "on the fbank stream (in the timed steps it overlaps the fbank kernels' tail on a second stream)"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps,
                     "h2d_bytes_per_step": int(a.calls * 2 * a.call_seconds * 8000 * 4),
-                    "d2h_bytes_per_step": int(2 * n_chunks * (38 * 4 + 4)), "checksum": checksum},
+                    "d2h_bytes_per_step": int(2 * n_chunks * (38 * 4 + 4)), "checksum": checksum,
+                    "host_planning": "inside the timed steps (plan cache cleared every step)",
+                    "h2d_floor_ms": ms_h2d,
+                    "h2d_floor_note": "upload only of the same pinned buffers, one cudaMemcpyAsync per call, all ranks at once; "
+                                      "best of 3, max over ranks",
+                    "h2d_floor_frac": ms_h2d / (ms_e2e / a.steps)},
             "e2e_wav16": {"value": total_hours / (ms_pcm / 1e3), "unit": UNIT, "ms_per_step": ms_pcm / a.steps,
                           "h2d_bytes_per_step": int(a.calls * 2 * a.call_seconds * 8000 * 2),
                           "d2h_bytes_per_step": int(2 * n_chunks * (38 * 4 + 4)), "checksum": checksum_pcm,
@@ -331,20 +393,24 @@ def run_afe(a):
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None,
                          "traffic": (traffic_pf * frames_per_launch) if traffic_pf else None,
+                         "traffic_source": ("profiles/r02_fbank_cfg2_ncu_summary.json: dram__bytes_read+write of one fbank launch of "
+                                            "this step under ncu --set full, per frame x frames per launch") if traffic_pf else None,
                          "algorithmic_bytes_per_launch": frames_per_launch * FBANK_BYTES_PER_FRAME,
                          "launches_timed": fb_n, "avg_launch_ms": fb_ms / max(fb_n, 1),
                          "note": "fp64-issue-bound, not HBM-bound: see DESIGN.md section 5"},
             # the pipe that actually bounds the kernel: 283 FP64 warp-instructions per frame at the
             # measured 0.49 warp-instructions/clk/scheduler (profiles/r01_pipe_probe_b200.txt), 4 schedulers x SMs
             "roofline_fp64": fp64_roof(frames_per_launch, fb_ms / max(fb_n, 1), fe.num_sms, clocks.get("sm_mhz")),
+            # ... and the one that binds first: shared-memory wavefronts per frame from the same ncu capture
+            "roofline_smem": smem_roof(frames_per_launch, fb_ms / max(fb_n, 1), fe.num_sms, clocks.get("sm_mhz"),
+                                       ncu.get("smem_wavefronts_per_frame")),
             "roofline_other_kernels": other,
         }
         if world == 1 and not a.no_cpu_baseline:
             from oracle import libref
-            cores = os.cpu_count() or 1
-            v, wall, desc = libref.timed_sample(max(1, min(cores, 64)), calls_per_worker=3, seconds=60.0)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": max(1, min(cores, 64)), "kind": "port",
-                                    "sample": desc, "wall_s": wall}
+            workers, group, seconds = cpu_sample_config(a)
+            v, span, desc = libref.timed_sample(workers, calls_per_worker=group, seconds=seconds, grouped=True)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": workers, "kind": "port", "sample": desc, "wall_s": span}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:

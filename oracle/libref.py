@@ -130,47 +130,81 @@ def front_end_call(call: torch.Tensor, sample_rate: int, acoustic: bool = True, 
     return len(chunks), call.shape[1] / float(sample_rate)
 
 
-def _worker(args) -> float:
-    seeds, seconds, sample_rate, threads = args
+def front_end_group(calls: Sequence[torch.Tensor], sample_rate: int, acoustic: bool = True, batch_size: int = 16):
+    """The hot path over a GROUP of calls the way process_file_batch runs it: every call resampled / split, the
+    chunks of ALL calls pooled, length-sorted and featurised in batches of ``batch_size``
+    (audio_processor.py:170-181), acoustic features per agent / client chunk.  Returns the call seconds."""
+    pooled, seconds = [], 0.0
+    for i, call in enumerate(calls):
+        chunks, _, _ = split_audio(call, sample_rate, f"call{i}.wav")
+        pooled += chunks
+        seconds += call.shape[1] / float(sample_rate)
+    featurise_chunks(pooled, batch_size)
+    if acoustic:
+        for c in pooled:
+            acoustic_features(c["agent_waveform"], 16000)
+            acoustic_features(c["client_waveform"], 16000)
+    return seconds
+
+
+def _worker(args):
+    """(call seconds processed, seconds spent processing): synthesis of the calls is outside the timed span."""
+    seeds, seconds, sample_rate, threads, grouped = args
     torch.set_num_threads(threads)
     from audio_processor_b200 import synth
     total = 0.0
     calls = [synth.make_call(seconds, sample_rate, s, 2) for s in seeds]
     t0 = time.perf_counter()
-    for call in calls:
-        total += front_end_call(call, sample_rate)[1]
+    if grouped:
+        total = front_end_group(calls, sample_rate)
+    else:
+        for call in calls:
+            total += front_end_call(call, sample_rate)[1]
     return total, time.perf_counter() - t0
 
 
-def timed_sample(n_workers: int, calls_per_worker: int = 1, seconds: float = 60.0, sample_rate: int = 8000
-                 ) -> Tuple[float, float, str]:
-    """Whole calls per worker process on ``n_workers`` host processes (the fbank loop of the
-    reference is single-threaded Python, so process parallelism is the fair throughput).
-    Returns (audio_hours_per_sec, wall_seconds, description)."""
-    import multiprocessing as mp
-    jobs = [([9000 + w * calls_per_worker + i for i in range(calls_per_worker)], seconds, sample_rate, 1)
+def timed_sample(n_workers: int, calls_per_worker: int = 1, seconds: float = 60.0, sample_rate: int = 8000,
+                 grouped: bool = False, pool=None) -> Tuple[float, float, str]:
+    """``n_workers`` host processes x 1 thread (the fbank loop of the reference is single-threaded Python, so
+    process parallelism is the fair throughput).  ``grouped``: each worker runs its calls as ONE file batch --
+    chunks of all its calls bucketed together (cfg2 shape when calls_per_worker >= 16 and seconds = 300).
+    The time is taken INSIDE the workers (the slowest worker's processing span; synthesising the calls is not
+    timed).  Returns (audio_hours_per_sec, seconds, description).  ``pool``: a Pool from ``worker_pool``."""
+    jobs = [([9000 + w * calls_per_worker + i for i in range(calls_per_worker)], seconds, sample_rate, 1, grouped)
             for w in range(n_workers)]
-    ctx = mp.get_context("spawn")
-    # one thread per worker process for EVERY library: torch.set_num_threads does not reach numpy's BLAS
-    # (the mel matmul of transformers' spectrogram), and n_workers x n_cores BLAS threads oversubscribe the
-    # box (measured 6.6x slower).  The spawned children inherit these variables.
+    own = pool is None
+    if own:
+        pool = worker_pool(n_workers)
+    try:
+        res = pool.map(_worker, jobs)
+    finally:
+        if own:
+            pool.terminate()
+    audio_s = sum(r[0] for r in res)
+    span = max(r[1] for r in res)
+    how = "chunks of each process's calls pooled and bucketed in batches of 16" if grouped else "call by call"
+    desc = (f"{n_workers * calls_per_worker} synthetic {seconds:.0f} s stereo {sample_rate} Hz calls, "
+            f"{n_workers} processes x 1 thread x {calls_per_worker} calls ({how}), full front end "
+            f"(resample+split+chunk+fbank x3+acoustic x2), timed inside the workers")
+    return audio_s / 3600.0 / span, span, desc
+
+
+def worker_pool(n_workers: int, sample_rate: int = 8000):
+    """A warmed spawn pool: one thread per worker for EVERY library -- torch.set_num_threads does not reach numpy's
+    BLAS (the mel matmul of transformers' spectrogram), and n_workers x n_cores BLAS threads oversubscribe the box
+    (measured 6.6x slower).  The spawned children inherit the variables."""
+    import multiprocessing as mp
     keys = ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS")
     saved = {k: os.environ.get(k) for k in keys}
     for k in keys:
         os.environ[k] = "1"
     try:
-        with ctx.Pool(n_workers) as pool:
-            pool.map(_worker, [([1], 2.0, sample_rate, 1)] * n_workers)          # warm imports / caches
-            t0 = time.perf_counter()
-            res = pool.map(_worker, jobs)
-            wall = time.perf_counter() - t0
+        pool = mp.get_context("spawn").Pool(n_workers)
+        pool.map(_worker, [([1], 2.0, sample_rate, 1, False)] * n_workers)          # warm imports / caches
     finally:
         for k, v in saved.items():
             if v is None:
                 os.environ.pop(k, None)
             else:
                 os.environ[k] = v
-    audio_s = sum(r[0] for r in res)
-    desc = (f"{n_workers * calls_per_worker} synthetic {seconds:.0f} s stereo {sample_rate} Hz calls, "
-            f"{n_workers} processes x 1 thread, full front end (resample+split+chunk+fbank x3+acoustic x2)")
-    return audio_s / 3600.0 / wall, wall, desc
+    return pool
