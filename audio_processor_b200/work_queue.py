@@ -8,6 +8,11 @@ reduces across calls, so there is no collective on the data path.
   and a sum of the audio seconds, through ``torch.distributed`` (NCCL on GPUs, gloo on CPU).
 * ``MultiGpuQueue`` -- in-process alternative: one worker thread per visible GPU pulling
   calls dynamically from a shared queue (no 4-GPU cap, stragglers balance).
+* ``MultiGpuProcessQueue`` -- the same dynamic pull with one worker PROCESS per GPU, which is what the
+  reference's ``MultiGPUManager`` runs (one process per GPU, ``CUDA_VISIBLE_DEVICES`` set, ``gpu_index`` 0:
+  multi_gpu_manager.py:298, 341).  Measured on 8 x B200 (profiles/r02_cfg4_queue.md): the thread variant
+  stops scaling at 2 GPUs because the Python side of every batch (planning, ctypes calls) holds the GIL;
+  processes scale like ``torchrun``.
 * ``ProcessedMarkers`` -- the ``<stem>.done`` / ``<stem>.failed`` marker files of
   ``DataProcessor`` (services/pipeline.py:280-315), same names and contents, so a run can be
   resumed by either implementation.
@@ -104,6 +109,116 @@ class MultiGpuQueue:
         if errors:
             raise errors[0]
         return out
+
+
+def _process_worker(dev, init_fn, init_args, fn, tasks, results):
+    """Body of one MultiGpuProcessQueue worker: binds the process to its GPU the way the reference does
+    (CUDA_VISIBLE_DEVICES before the first CUDA call, device index 0 inside), builds its state once, then pulls
+    ``(index, item)`` pairs until the ``None`` sentinel."""
+    import os
+    import traceback
+    try:
+        if dev is not None:
+            os.environ["CUDA_VISIBLE_DEVICES"] = str(dev)
+        state = init_fn(dev, *init_args) if init_fn is not None else None
+        results.put(("ready", dev, None))
+    except BaseException as e:                       # noqa: BLE001
+        results.put(("dead", dev, f"{e!r}\n{traceback.format_exc()}"))
+        return
+    while True:
+        task = tasks.get()
+        if task is None:
+            return
+        i, item = task
+        try:
+            results.put(("ok", i, fn(state, item)))
+        except BaseException as e:                   # noqa: BLE001
+            results.put(("err", i, f"{e!r}\n{traceback.format_exc()}"))
+
+
+class MultiGpuProcessQueue:
+    """Host work queue over one worker process per GPU, dynamic pull, any GPU count::
+
+        with MultiGpuProcessQueue(devices, init_fn, init_args) as q:     # init_fn(dev, *init_args) -> state, once per worker
+            results = q.map(fn, items)                                   # fn(state, item); results keep the input order
+
+    ``init_fn`` / ``fn`` are module-level functions (the workers are spawned).  Inside a worker the GPU is device 0
+    (``CUDA_VISIBLE_DEVICES`` = the physical index, as multi_gpu_manager.py:298 does); a ``None`` device binds nothing
+    (CPU tests).  An item that raises is reported after the map as ``RuntimeError`` carrying the worker's traceback;
+    the other items still run.  With ``markers`` the reference's per-file contract applies in the parent: ``.done``
+    files are skipped, successes marked ``.done``, failures ``.failed`` (no exception then)."""
+
+    def __init__(self, devices: Optional[Sequence[Optional[int]]] = None, init_fn: Optional[Callable] = None,
+                 init_args: tuple = ()):
+        if devices is None:
+            import torch
+            devices = list(range(torch.cuda.device_count()))
+        if not devices:
+            raise RuntimeError("MultiGpuProcessQueue needs at least one device")
+        self.devices = list(devices)
+        self._init = (init_fn, tuple(init_args))
+        self._procs: list = []
+        self._tasks = self._results = None
+        self._fn = None
+
+    def start(self, fn: Callable) -> "MultiGpuProcessQueue":
+        import multiprocessing as mp
+        if self._procs:
+            if fn is not self._fn:
+                raise RuntimeError("the workers were started with another function")
+            return self
+        ctx = mp.get_context("spawn")
+        self._tasks, self._results, self._fn = ctx.Queue(), ctx.Queue(), fn
+        for d in self.devices:
+            p = ctx.Process(target=_process_worker, args=(d, self._init[0], self._init[1], fn, self._tasks, self._results),
+                            daemon=True)
+            p.start()
+            self._procs.append(p)
+        for _ in self.devices:
+            kind, dev, msg = self._results.get()
+            if kind != "ready":
+                self.close()
+                raise RuntimeError(f"worker of device {dev} failed to start: {msg}")
+        return self
+
+    def map(self, fn: Callable, items: Sequence, markers: "Optional[ProcessedMarkers]" = None) -> List:
+        self.start(fn)
+        todo = [(i, it) for i, it in enumerate(items) if not (markers is not None and markers.is_already_processed(it))]
+        for t in todo:
+            self._tasks.put(t)
+        out: List = [None] * len(items)
+        errors = []
+        for _ in todo:
+            kind, i, payload = self._results.get()
+            if kind == "ok":
+                out[i] = payload
+                if markers is not None:
+                    markers.mark_file_processed(items[i])
+            elif markers is not None:
+                markers.mark_file_failed(items[i], str(payload).splitlines()[0])
+            else:
+                errors.append((i, payload))
+        if errors:
+            raise RuntimeError(f"item {errors[0][0]} failed in its worker: {errors[0][1]}")
+        return out
+
+    def close(self) -> None:
+        for _ in self._procs:
+            try:
+                self._tasks.put(None)
+            except Exception:
+                pass
+        for p in self._procs:
+            p.join(timeout=10)
+            if p.is_alive():
+                p.terminate()
+        self._procs = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 class ProcessedMarkers:
