@@ -40,6 +40,21 @@ def _tempo(flux_energy: float, num_samples: int, sample_rate: int) -> float:
     return 60.0 / period if period > 0 else 0.0
 
 
+_NO_AUDIO = torch.zeros(0, dtype=torch.float32)
+
+
+def _as_reference_mono(w):
+    """What ``waveform.squeeze(0)`` followed by ``unfold(0, 400, 160)`` accepts in the reference (:813-823): a 1-D
+    signal or a ``(1, L)`` tensor.  Anything else -- ``(2, L)`` stereo, ``(1, 1, L)`` -- makes ``unfold`` raise there,
+    which the reference turns into ``None`` / the zero feature vector; an empty signal gives the same result here."""
+    shape = tuple(w.shape)
+    if len(shape) == 1:
+        return w
+    if len(shape) == 2 and shape[0] == 1:
+        return w[0]
+    return _NO_AUDIO
+
+
 def extract_acoustic_features_batch(waveforms: Sequence, sample_rate: int = 16000, device=None
                                     ) -> List[Optional["OrderedDict[str, float]"]]:
     """One ordered dict of 38 Python floats per waveform, ``None`` where the reference
@@ -47,7 +62,8 @@ def extract_acoustic_features_batch(waveforms: Sequence, sample_rate: int = 1600
     if not waveforms:
         return []
     fe = runtime.get_frontend(device)
-    rows, status = fe.acoustic(list(waveforms), sample_rate)
+    waveforms = [_as_reference_mono(w) for w in waveforms]
+    rows, status = fe.acoustic(waveforms, sample_rate)
     rows = rows.cpu()
     status = status.cpu().tolist()
     values = rows.tolist()
@@ -140,7 +156,7 @@ class AcousticSentimentAnalyzer(AcousticFeatureExtractor):
     def _scaled_features(self, waveforms: Sequence[torch.Tensor], sample_rate: int, scaler):
         """``acoustic_scaler.transform(feature_lists)`` of :736-752 as a float64 numpy matrix."""
         fe = runtime.get_frontend(self.device)
-        dev_waves, lens = fe._to_device_1d([w.reshape(-1) for w in waveforms])
+        dev_waves, lens = fe._to_device_1d([_as_reference_mono(w) for w in waveforms])
         _, _, scaled = fe.acoustic_ptrs([t.data_ptr() if t.numel() else 0 for t in dev_waves], lens, sample_rate,
                                         scaler=self._scaler_vectors(scaler))
         return scaled.cpu().numpy()

@@ -439,3 +439,17 @@ def test_fbank_aligned_and_unaligned_tiles_alternate_within_a_block(fe):
     for i in (0, 1, 2, 151, 299):
         ref_f, _ = np_fbank.featurise([views[i].cpu().numpy()])
         _cmp_nan(f1[i:i + 1].cpu().numpy(), ref_f, 1e-3)
+
+
+def test_acoustic_shape_rule_is_the_reference_squeeze0(fe, golden):
+    """``waveform.squeeze(0)`` + ``unfold(0, ...)`` of the reference accepts (L,) and (1, L); a (2, L) or (1, 1, L)
+    tensor makes it raise -> None -> zero features.  Same here, on both entry paths."""
+    import torch
+    from audio_processor_b200 import acoustic
+    w = torch.from_numpy(golden("acoustic")["speech_8000_wave"]).to(fe.device)
+    stereo = torch.stack([w, w.flip(0)])
+    feats = acoustic.extract_acoustic_features_batch([w, w[None], stereo, w[None, None]], 16000, fe.device)
+    assert feats[0] is not None and feats[0] == feats[1] and feats[2] is None and feats[3] is None
+    ex = acoustic.AcousticFeatureExtractor(fe.device)
+    assert ex._extract_acoustic_features(stereo, 16000) is None
+    assert ex.extract_batch([w[None], stereo], 16000)[1] == [0.0] * 38
