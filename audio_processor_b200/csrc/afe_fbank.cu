@@ -5,12 +5,24 @@
 
 #include "afe_ctx.h"
 #include "afe_fbank_kernels.h"
+#include "afe_fbank_pipe.h"
 
 using namespace afe;
 
 namespace {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// AFE_FBANK_PIPE=1 selects the three-group tile pipeline (afe_fbank_pipe.h, 16-frame tiles) instead of the
+// phase-serial kernel (32-frame tiles); read once per process.  Both give bit-identical features.
+#ifndef AFE_FBANK_PIPE_DEFAULT
+#define AFE_FBANK_PIPE_DEFAULT 0
+#endif
+bool use_pipe() {
+  static const bool on = [] { const char* e = std::getenv("AFE_FBANK_PIPE"); return e ? e[0] == '1' : (AFE_FBANK_PIPE_DEFAULT != 0); }();
+  return on;
+}
+int fbank_tile() { return use_pipe() ? kPipeTile : kFbTile; }
 
 // workspace layout (device): [descriptors][partials: ntiles*80*2 f64][stats: B*80*2 f32]
 struct FbankLayout {
@@ -26,7 +38,7 @@ FbankLayout fbank_layout(const int64_t* lengths, int B) {
   l.B = B;
   for (int b = 0; b < B; ++b) {
     const int64_t T = afe_fbank_num_frames(lengths[b]);
-    l.ntiles += (long)((T + kFbTile - 1) / kFbTile);
+    l.ntiles += (long)((T + fbank_tile() - 1) / fbank_tile());
   }
   size_t o = 0;
   l.off_wave = o;   o = align_up(o + sizeof(void*) * (size_t)B, 16);
@@ -47,12 +59,20 @@ FbankLayout fbank_layout(const int64_t* lengths, int B) {
 template <typename T>
 int run_fbank(afe_ctx* ctx, cudaStream_t s, const BatchDesc& d, float* feat, double* partials,
               const T* window, const T* tw, int32_t* mask, float padding_value) {
+  ProfScope ps(ctx, AFE_K_FBANK, s);
+  if (use_pipe()) {
+    FbankPipeKernel<T> k;
+    k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
+    k.mask = mask; k.padding_value = padding_value;
+    k.log_floor = ctx->log_floor;
+    k.mel_w = ctx->kaldi_slots.w; k.mel_start = ctx->kaldi_slots.start;
+    return afe_launch_fbank_pipe(k, ctx->num_sms, s);
+  }
   FbankKernel<T> k;
   k.d = d; k.out = feat; k.partials = partials; k.window = window; k.tw512 = tw;
   k.mask = mask; k.padding_value = padding_value;
   k.log_floor = ctx->log_floor;
   k.mel_w = ctx->kaldi_slots.w; k.mel_start = ctx->kaldi_slots.start;
-  ProfScope ps(ctx, AFE_K_FBANK, s);
   return afe_launch(k, FbankKernel<T>::S::kBytes, ctx->num_sms * FbankKernel<T>::kMinBlocks, s);
 }
 
@@ -108,7 +128,7 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
   // into one block is normalised by that block right after its last tile (its raw rows are still
   // in L2); the others -- at most one per block boundary -- and those without frames go to the
   // stats / norm kernels.
-  const long grid = afe_async_grid(l.ntiles, ctx->num_sms * FbankKernel<double>::kMinBlocks);
+  const long grid = afe_async_grid(l.ntiles, use_pipe() ? ctx->num_sms : ctx->num_sms * FbankKernel<double>::kMinBlocks);
   const long per = grid > 0 ? (l.ntiles + grid - 1) / grid : 1;
   int nsel = 0;
   int64_t acc = 0, rows = 0, tp_max = 0;
@@ -119,7 +139,7 @@ int fbank_run(afe_ctx* ctx, void* stream, const float* const* h_waves, const int
     if (T > 0 && !h_waves[b]) bad = true;
     if (tp < T || (tp & 1) || rows_of[b] < 0 || (rows_of[b] & 1)) bad = true;
     hw[b] = h_waves[b]; hl[b] = h_lengths[b]; hf[b] = (int32_t)T; hp[b] = acc; hr[b] = rows_of[b]; ht[b] = (int32_t)tp;
-    const int64_t nt = (T + kFbTile - 1) / kFbTile;
+    const int64_t nt = (T + fbank_tile() - 1) / fbank_tile();
     const bool whole = !raw_only && nt > 0 && (acc / per) == ((acc + nt - 1) / per);
     hwh[b] = whole ? 1 : 0;
     if (!whole) { hsel[nsel++] = b; tp_max = std::max(tp_max, tp); }
@@ -257,7 +277,7 @@ int afe_fbank_batch_static(afe_ctx* ctx, void* stream, const float* const* h_wav
   const FbankLayout l = fbank_layout(h_lengths, batch);
   if (l.total > kStaticScratchBytes)
     return fail(AFE_ERR_WORKSPACE, "afe_fbank_batch_static: the batch needs " + std::to_string(l.total) + " bytes of scratch, the static array holds " +
-                                       std::to_string(kStaticScratchBytes) + " (about " + std::to_string(kStaticScratchBytes / (2 * kMel * sizeof(double)) * kFbTile / 100) +
+                                       std::to_string(kStaticScratchBytes) + " (about " + std::to_string(kStaticScratchBytes / (2 * kMel * sizeof(double)) * fbank_tile() / 100) +
                                        " s of audio per call); use afe_fbank_batch with a caller workspace");
   if (!ctx->fbank_static_scratch) return fail(AFE_ERR_CUDA, "afe_fbank_batch_static: the static scratch was not set up for this device");
   // descriptors and placement on the stack: no pinned pool, no heap block whose size depends on the call

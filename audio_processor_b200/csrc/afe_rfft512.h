@@ -115,17 +115,15 @@ AFE_HD float rfft_mag(float p) {
 }
 
 // kMag: also store the magnitude sqrt(power) to sM (same layout as sP)
+// v[n2] = the exchange values ex[(role * 16 + n2) * TF + f] of (role, frame), already in registers
 template <typename T, bool kMag = false, int TF = kTileFrames>
-AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, float* AFE_RESTRICT sP,
-                           float* AFE_RESTRICT sM = nullptr) {
+AFE_HD void rfft512_stage2_regs(int role, int f, const cplx<T> (&v)[16], float* AFE_RESTRICT sP,
+                                float* AFE_RESTRICT sM = nullptr) {
 #define AFE_PUT(bin, val) { const float p_ = (float)(val); sP[(bin) * TF + f] = p_; if (kMag) sM[(bin) * TF + f] = rfft_mag(p_); }
   if (role != 0) {
     T re[16], im[16];
 #pragma unroll
-    for (int n2 = 0; n2 < 16; ++n2) {
-      const cplx<T> v = ex[(role * 16 + n2) * TF + f];
-      re[n2] = v.re; im[n2] = v.im;
-    }
+    for (int n2 = 0; n2 < 16; ++n2) { re[n2] = v[n2].re; im[n2] = v[n2].im; }
     fft16(re, im);
 #pragma unroll
     for (int k2 = 0; k2 < 16; ++k2) {
@@ -137,10 +135,7 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
   // role 0: row k1 = 0 (real input a0) and row k1 = 16 (real input a16, half-bin shifted)
   T a0[16], a16[16];
 #pragma unroll
-  for (int n2 = 0; n2 < 16; ++n2) {
-    const cplx<T> v = ex[(0 * 16 + n2) * TF + f];
-    a0[n2] = v.re; a16[n2] = v.im;
-  }
+  for (int n2 = 0; n2 < 16; ++n2) { a0[n2] = v[n2].re; a16[n2] = v[n2].im; }
   {
     T re[8], im[8];
 #pragma unroll
@@ -180,5 +175,14 @@ AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, floa
   }
 }
 #undef AFE_PUT
+
+template <typename T, bool kMag = false, int TF = kTileFrames>
+AFE_HD void rfft512_stage2(int role, int f, const cplx<T>* AFE_RESTRICT ex, float* AFE_RESTRICT sP,
+                           float* AFE_RESTRICT sM = nullptr) {
+  cplx<T> v[16];
+#pragma unroll
+  for (int n2 = 0; n2 < 16; ++n2) v[n2] = ex[(role * 16 + n2) * TF + f];
+  rfft512_stage2_regs<T, kMag, TF>(role, f, v, sP, sM);
+}
 
 }  // namespace afe

@@ -19,7 +19,7 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 SOURCES = ["afe_runtime.cu", "afe_host.cc", "afe_tables.cc", "afe_resample.cu", "afe_fbank.cu", "afe_acoustic.cu"]
 HEADERS = ["afe_platform.h", "afe_fft.h", "afe_rfft512.h", "afe_tables.h", "afe_ctx.h", "afe_fbank_kernels.h",
-           "afe_resample_kernels.h", "afe_acoustic_kernels.h", "afe_dct_gen.h", "afe_mel_slots.h", os.path.join(ROOT, "include", "afe.h")]
+           "afe_fbank_pipe.h", "afe_resample_kernels.h", "afe_acoustic_kernels.h", "afe_dct_gen.h", "afe_mel_slots.h", os.path.join(ROOT, "include", "afe.h")]
 CUDA_LIB = os.path.join(PKG, "libafe.so")
 EMU_LIB = os.path.join(ROOT, "tests", "_emu", "libafe_emu.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

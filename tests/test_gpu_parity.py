@@ -453,3 +453,40 @@ def test_acoustic_shape_rule_is_the_reference_squeeze0(fe, golden):
     ex = acoustic.AcousticFeatureExtractor(fe.device)
     assert ex._extract_acoustic_features(stereo, 16000) is None
     assert ex.extract_batch([w[None], stereo], 16000)[1] == [0.0] * 38
+
+
+def test_fbank_pipeline_kernel_is_bit_identical_to_the_serial_one(fe, tmp_path):
+    """AFE_FBANK_PIPE=1 selects the three-group tile pipeline (csrc/afe_fbank_pipe.h, 16-frame tiles, named
+    barriers); the switch is read once per process, so the pipeline runs in a child process on the same seeded
+    batch (ragged, grouped, silence, unaligned views, an utterance spanning several blocks) and must reproduce
+    the serial kernel's features and masks bit for bit."""
+    import os
+    import subprocess
+    import sys
+    script = tmp_path / "pipe_case.py"
+    script.write_text('''
+import sys, numpy as np, torch
+sys.path.insert(0, sys.argv[1])
+from audio_processor_b200 import runtime
+fe = runtime.get_frontend(0)
+g = torch.Generator().manual_seed(99)
+base = (torch.rand(3_000_000, generator=g) - 0.5).to(fe.device)
+lens = [400_000, 399, 400, 16_000, 123_457, 720, 48_000, 1_500_001, 30_000, 250_001]
+waves, off = [], 0
+for i, n in enumerate(lens):
+    waves.append(base[off + (i % 3):off + (i % 3) + n]); off += n + 8
+waves[4] = torch.zeros(123_457, device=fe.device)
+outs = fe.fbank(waves, group_size=4)
+f = torch.cat([a.reshape(-1) for a, _ in outs]).cpu().numpy(); m = torch.cat([b.reshape(-1) for _, b in outs]).cpu().numpy()
+np.savez(sys.argv[2], f=f, m=m)
+''')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for mode in ("0", "1"):
+        out = tmp_path / f"mode{mode}.npz"
+        env = {**os.environ, "AFE_FBANK_PIPE": mode}
+        subprocess.run([sys.executable, str(script), root, str(out)], check=True, env=env, timeout=300)
+        res[mode] = np.load(out)
+    assert np.array_equal(res["0"]["m"], res["1"]["m"])
+    assert np.array_equal(res["0"]["f"], res["1"]["f"], equal_nan=True)
+    assert np.isfinite(res["1"]["f"][np.repeat(res["1"]["m"], 160) == 1]).all()
