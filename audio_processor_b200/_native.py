@@ -155,10 +155,15 @@ def load() -> Library:
 
 
 def i64_array(values):
-    arr = (C.c_int64 * len(values))(*[int(v) for v in values])
-    return arr
+    """ctypes ``int64[n]`` over a numpy buffer (a ctypes splat of a Python list costs 4x as much; these arrays carry
+    thousands of chunk lengths / rows per launch and sit on the host's critical path)."""
+    import numpy as np
+    buf = np.array(values, dtype=np.int64).reshape(-1) if len(values) else np.zeros(1, np.int64)
+    return (C.c_int64 * max(len(values), 1)).from_buffer(buf)
 
 
 def ptr_array(values):
-    arr = (C.c_void_p * len(values))(*[C.c_void_p(int(v)) for v in values])
-    return arr
+    """ctypes ``void*[n]`` of device / host addresses given as Python ints (0 = NULL)."""
+    import numpy as np
+    buf = np.array(values, dtype=np.uint64).reshape(-1) if len(values) else np.zeros(1, np.uint64)
+    return (C.c_void_p * max(len(values), 1)).from_buffer(buf)
