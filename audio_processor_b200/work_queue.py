@@ -175,7 +175,7 @@ class MultiGpuProcessQueue:
             p.start()
             self._procs.append(p)
         for _ in self.devices:
-            kind, dev, msg = self._results.get()
+            kind, dev, msg = self._next_result()
             if kind != "ready":
                 self.close()
                 raise RuntimeError(f"worker of device {dev} failed to start: {msg}")
@@ -189,7 +189,7 @@ class MultiGpuProcessQueue:
         out: List = [None] * len(items)
         errors = []
         for _ in todo:
-            kind, i, payload = self._results.get()
+            kind, i, payload = self._next_result()
             if kind == "ok":
                 out[i] = payload
                 if markers is not None:
@@ -201,6 +201,19 @@ class MultiGpuProcessQueue:
         if errors:
             raise RuntimeError(f"item {errors[0][0]} failed in its worker: {errors[0][1]}")
         return out
+
+    def _next_result(self):
+        """Next message of a worker; a worker that died without one (segfault, OOM kill) must not hang the parent."""
+        import queue as _queue
+        while True:
+            try:
+                return self._results.get(timeout=1.0)
+            except _queue.Empty:
+                dead = [p for p in self._procs if not p.is_alive()]
+                if dead:
+                    codes = ", ".join(str(p.exitcode) for p in dead)
+                    self.close()
+                    raise RuntimeError(f"{len(dead)} worker process(es) died (exit code {codes}) with work outstanding")
 
     def close(self) -> None:
         for _ in self._procs:

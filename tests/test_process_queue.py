@@ -44,3 +44,17 @@ def test_process_queue_markers(tmp_path):
         assert (tmp_path / "a.done").exists() and (tmp_path / "c.done").exists()
         assert "cannot decode" in (tmp_path / "boom.failed").read_text()
         assert q.map(_work, files, markers=markers) == [None, None, None]      # .done files are skipped, boom fails again
+
+
+def _die(state, item):
+    if item == 2:
+        os._exit(7)                                # a worker that vanishes without a message (segfault, OOM kill)
+    time.sleep(0.05)
+    return item
+
+
+def test_process_queue_reports_a_dead_worker_instead_of_hanging():
+    q = MultiGpuProcessQueue([None, None], _init, ("d",))
+    with pytest.raises(RuntimeError, match="died"):
+        q.map(_die, list(range(6)))
+    q.close()
