@@ -61,12 +61,15 @@ struct AcSmem {
   static constexpr size_t kPfOff = kRedOff + sizeof(float) * kPS;
   static constexpr size_t kThrOff = kPfOff + sizeof(float) * 8 * 32;
   static constexpr size_t kDsumOff = kThrOff + sizeof(float) * 64;                   // float thr[32] | int rc[32] at kThrOff, double lo[32] here: the rolloff hand-over
+  // int64 stash[2]: the tile whose record is still owed {item index + 1 (0: none), n1 | nvalid << 16} -- written in the last
+  // phase of a tile, consumed by warps 11..15 in phase 1 of the block's next tile (or by block_flush after its last)
+  static constexpr size_t kStashOff = kDsumOff + sizeof(double) * 32;
   static constexpr size_t kHannOff = kExOff + sizeof(cplx<float>) * 16 * 16 * kTileFrames;   // float hann[16][26] (block_init)
   static constexpr size_t kTwOff = kHannOff + sizeof(float) * kRoles * kWinRow;               // float tw512[16][16][2]
   static constexpr size_t kMelWOff = (kTwOff + sizeof(float) * kRoles * 32 + 15) / 16 * 16;      // float melw[16][40] slot-form HTK bank (block_init)
   static constexpr size_t kMelSOff = kMelWOff + sizeof(float) * kRoles * kMelSlotRow;            // int32 mels[16][8]
   static constexpr size_t kBytes = kMelSOff + sizeof(int32_t) * kRoles * kMelSlotStarts;
-  static_assert(kDsumOff % 8 == 0 && kDsumOff + sizeof(double) * 32 <= kHannOff, "ex region too small");
+  static_assert(kDsumOff % 8 == 0 && kStashOff + 16 <= kHannOff, "ex region too small");
 };
 
 // sqrt for magnitudes: one MUFU (max relative error ~1 ulp); the reference's float32 |X| carries
@@ -84,8 +87,9 @@ AFE_HD float mag_sqrt(float x) {
 struct AcousticTileKernel {
   static constexpr int kThreads = 512;
   static constexpr int kMinBlocks = 1;
-  static constexpr int kPhases = 7;
+  static constexpr int kPhases = 6;
   static constexpr int kTailPhases = 0;
+  static constexpr int kRecordWarp0 = 11;                 // warps 11..15 have no 16-sample groups in phase 1
   static constexpr bool kAsyncStage = true;
   static constexpr int kRS = AcSmem::kRS, kPS = AcSmem::kPS;
   static constexpr size_t kStageOff = AcSmem::kRawOff;
@@ -114,7 +118,10 @@ struct AcousticTileKernel {
     int32_t* ms = reinterpret_cast<int32_t*>(smem + AcSmem::kMelSOff);
     for (int i = tid; i < kRoles * kMelSlotRow; i += kThreads) mw[i] = ldg(mel_w + i);
     for (int i = tid; i < kRoles * kMelSlotStarts; i += kThreads) ms[i] = ldg(mel_start + i);
+    if (tid == 0) reinterpret_cast<int64_t*>(smem + AcSmem::kStashOff)[0] = 0;      // no record owed yet
   }
+  // the record of the block's last tile (every other tile's is written under phase 1 of the tile after it)
+  AFE_HD void block_flush(unsigned char* smem, int tid) const { owed_record(smem, tid); }
 
   AFE_HD Item prepare(long item) const {
     Item it;
@@ -182,6 +189,68 @@ struct AcousticTileKernel {
     }
     if (rc == 15) below += ((float)(acc + nonneg_to_double(mp[16 * kTileFrames])) < thr) ? 1 : 0;   // bin 256
     return 31.25f * (float)(16 * rc + below);
+  }
+
+  // ---- tile record: one warp per statistic (lane = frame, fixed-tree reductions); statistic 4 (rolloff) first finds the
+  // crossing bin inside the role phase 5 located.  0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff: (sum, sum sq);
+  // 5 flux energy; 6 rms range; 7 max dB.  Reads pf / the rolloff hand-over / sM of the tile it belongs to, which stay
+  // untouched until phase 3 / phase 5 of the next tile.
+  AFE_HD void record_stat(int stat, int f, long rec_item, int n1, int nvalid, unsigned char* smem) const {
+    const float* sM = reinterpret_cast<const float*>(smem + AcSmem::kMOff);
+    const float* roll_thr = reinterpret_cast<const float*>(smem + AcSmem::kThrOff);
+    const int* roll_rc = reinterpret_cast<const int*>(smem + AcSmem::kThrOff) + 32;
+    const double* roll_lo = reinterpret_cast<const double*>(smem + AcSmem::kDsumOff);
+    const float* pf = reinterpret_cast<const float*>(smem + AcSmem::kPfOff);
+    double* rec = tile_rec + rec_item * kTileRec;
+    const int src = (stat == 0) ? 4 : (stat == 1) ? 5 : (stat < 5) ? (stat - 2) : (stat == 5) ? 3 : (stat == 6) ? 4 : 6;
+    const int n = (stat < 2 || stat == 6) ? n1 : (stat == 5) ? nvalid - 1 : nvalid;
+#if AFE_CUDA && defined(__CUDA_ARCH__)
+    const double v = (double)((stat == 4) ? rolloff_bin(sM, roll_rc[f], roll_lo[f], roll_thr[f], f) : pf[src * 32 + f]);
+    if (stat < 6) {
+      const double x = (f < n) ? v : 0.0;
+      const double s = warp_tree_sum(x), ss = warp_tree_sum(x * x);
+      if (f == 0) {
+        if (stat < 5) { rec[2 * stat] = s; rec[2 * stat + 1] = ss; } else rec[10] = ss;
+      }
+    } else if (stat == 6) {
+      const double mn = warp_tree_min((f < n) ? v : 3.0e38), mxv = warp_tree_max((f < n) ? v : -3.0e38);
+      if (f == 0) { rec[11] = mn; rec[12] = mxv; }
+    } else {
+      const double mxv = warp_tree_max((f < n) ? v : -3.0e38);
+      if (f == 0) rec[13] = (double)(float)mxv;
+    }
+#else
+    if (f == 0) {   // host emulation: lane 0 walks the same trees
+      double a[32], q[32], mn = 3.0e38, mxv = -3.0e38;
+      for (int j = 0; j < 32; ++j) {
+        const double v = (j >= n) ? 0.0 : (double)((stat == 4) ? rolloff_bin(sM, roll_rc[j], roll_lo[j], roll_thr[j], j) : pf[src * 32 + j]);
+        a[j] = v; q[j] = v * v;
+        if (j < n) { mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv; }
+      }
+      if (stat < 5) { rec[2 * stat] = tree32_sum(a); rec[2 * stat + 1] = tree32_sum(q); }
+      else if (stat == 5) rec[10] = tree32_sum(q);
+      else if (stat == 6) { rec[11] = mn; rec[12] = mxv; }
+      else rec[13] = (double)(float)mxv;
+    }
+#endif
+  }
+  // the record the stash says is owed, by warps 11..15: 11 rolloff (the long dependent chain), 12: rms + zcr, 13: centroid +
+  // bandwidth, 14: flux + rms range, 15: max dB.  Warp-uniform branches only (the trees are full-warp shuffles).
+  AFE_HD void owed_record(unsigned char* smem, int tid) const {
+    const int w = tid >> 5, f = tid & 31;
+    if (w < kRecordWarp0) return;
+    const int64_t* stash = reinterpret_cast<const int64_t*>(smem + AcSmem::kStashOff);
+    const int64_t owed = stash[0];
+    if (owed == 0) return;
+    const int n1 = (int)(stash[1] & 0xffff), nvalid = (int)(stash[1] >> 16);
+    const long rec_item = (long)(owed - 1);
+    switch (w - kRecordWarp0) {
+      case 0: record_stat(4, f, rec_item, n1, nvalid, smem); break;
+      case 1: record_stat(0, f, rec_item, n1, nvalid, smem); record_stat(1, f, rec_item, n1, nvalid, smem); break;
+      case 2: record_stat(2, f, rec_item, n1, nvalid, smem); record_stat(3, f, rec_item, n1, nvalid, smem); break;
+      case 3: record_stat(5, f, rec_item, n1, nvalid, smem); record_stat(6, f, rec_item, n1, nvalid, smem); break;
+      default: record_stat(7, f, rec_item, n1, nvalid, smem); break;
+    }
   }
 
   AFE_HD void phase(int ph, const Item& it, unsigned char* smem, int tid) const {
@@ -289,6 +358,9 @@ struct AcousticTileKernel {
         }
         if (tid < kTileFrames)     // the pair (-1, 0) of unfold frame tid is counted by its first group but is NOT part of the frame
           lastx[tid] = crossing(raw[200 + kHop * tid - 1], raw[200 + kHop * tid]) ? 1.f : 0.f;
+        // the record of the block's PREVIOUS tile, by the warps that have no groups above: a one-warp dependent chain
+        // (rolloff) that used to be a phase of its own with 15 warps waiting at its barrier
+        owed_record(smem, tid);
       } break;
       case 2: {   // Hann window + stage 1 of the real FFT
         float r[25];
@@ -420,44 +492,11 @@ struct AcousticTileKernel {
             boundary[(it.item * 2 + second) * kBoundary + k] = sM[k * kTileFrames + (second ? it.nvalid - 1 : 0)];
           }
         }
-      } break;
-      case 6: {   // tile record (one warp per statistic, lane = frame, fixed-tree reductions); the rolloff warp first
-                  // finds the crossing bin inside the role phase 5 located
-        double* rec = tile_rec + it.item * kTileRec;
-        if (role < 8) {
-          // 0 rms 1 zcr (unfold frames) 2 centroid 3 bandwidth 4 rolloff: (sum, sum sq); 5 flux energy; 6 rms range; 7 max dB
+        if (tid == kThreads - 1) {              // this tile's record is owed: stash what it needs (consumed after the barrier)
+          int64_t* stash = reinterpret_cast<int64_t*>(smem + AcSmem::kStashOff);
           const int n1 = tmax(0, tmin(kTileFrames, it.F1 - it.f0));
-          const int src = (role == 0) ? 4 : (role == 1) ? 5 : (role < 5) ? (role - 2) : (role == 5) ? 3 : (role == 6) ? 4 : 6;
-          const int n = (role < 2 || role == 6) ? n1 : (role == 5) ? it.nvalid - 1 : it.nvalid;
-#if AFE_CUDA && defined(__CUDA_ARCH__)
-          const double v = (double)((role == 4) ? rolloff_bin(sM, roll_rc[f], roll_lo[f], roll_thr[f], f) : pf[src * 32 + f]);
-          if (role < 6) {
-            const double x = (f < n) ? v : 0.0;
-            const double s = warp_tree_sum(x), ss = warp_tree_sum(x * x);
-            if (f == 0) {
-              if (role < 5) { rec[2 * role] = s; rec[2 * role + 1] = ss; } else rec[10] = ss;
-            }
-          } else if (role == 6) {
-            const double mn = warp_tree_min((f < n) ? v : 3.0e38), mxv = warp_tree_max((f < n) ? v : -3.0e38);
-            if (f == 0) { rec[11] = mn; rec[12] = mxv; }
-          } else {
-            const double mxv = warp_tree_max((f < n) ? v : -3.0e38);
-            if (f == 0) rec[13] = (double)(float)mxv;
-          }
-#else
-          if (f == 0) {   // host emulation: lane 0 walks the same trees
-            double a[32], q[32], mn = 3.0e38, mxv = -3.0e38;
-            for (int j = 0; j < 32; ++j) {
-              const double v = (j >= n) ? 0.0 : (double)((role == 4) ? rolloff_bin(sM, roll_rc[j], roll_lo[j], roll_thr[j], j) : pf[src * 32 + j]);
-              a[j] = v; q[j] = v * v;
-              if (j < n) { mn = v < mn ? v : mn; mxv = v > mxv ? v : mxv; }
-            }
-            if (role < 5) { rec[2 * role] = tree32_sum(a); rec[2 * role + 1] = tree32_sum(q); }
-            else if (role == 5) rec[10] = tree32_sum(q);
-            else if (role == 6) { rec[11] = mn; rec[12] = mxv; }
-            else rec[13] = (double)(float)mxv;
-          }
-#endif
+          stash[0] = (int64_t)it.item + 1;
+          stash[1] = (int64_t)n1 | ((int64_t)it.nvalid << 16);
         }
       } break;
     }

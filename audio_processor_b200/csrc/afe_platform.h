@@ -251,6 +251,14 @@ struct has_block_init<K, decltype(std::declval<const K&>().block_init((unsigned 
   static constexpr bool value = true;
 };
 
+// optional per-block epilogue  void block_flush(unsigned char* smem, int tid) const  -- work a kernel deferred from its last
+// item into "the next item's first phase" (AcousticTileKernel: the tile record), run once after the block's last item
+template <class K, class = void> struct has_block_flush { static constexpr bool value = false; };
+template <class K>
+struct has_block_flush<K, decltype(std::declval<const K&>().block_flush((unsigned char*)nullptr, 0))> {
+  static constexpr bool value = true;
+};
+
 // the thread that derives the next item and issues its TMA copy while the block works on the current
 // one: K::kPrefetchThread if the kernel names a thread whose warp idles in phase 1, else thread 0
 // optional two-segment staging  bool stage_src2(const Item&, const float* (&src)[2], int (&nfloats)[2], int (&dst_float_off)[2]) const
@@ -425,6 +433,7 @@ __global__ void __launch_bounds__(K::kThreads, K::kMinBlocks) phased_kernel(cons
         }
       }
     }
+    if constexpr (has_block_flush<K>::value) k.block_flush(afe_smem, tid);     // the last item's barrier has been passed
     if constexpr (kTrace) {     // lane 0 of every warp: trace[(block * 32 + warp) * 16 + slot]
       if ((tid & 31) == 0) for (int i = 0; i < 24; ++i) trace[((size_t)blockIdx.x * 32 + (tid >> 5)) * 24 + i] = (unsigned long long)tacc[i];
     }
@@ -541,6 +550,8 @@ int afe_launch(const K& k, size_t smem_bytes, int max_blocks, cudaStream_t) {
               for (int tid = 0; tid < K::kThreads; ++tid) k.phase(ph, ic, smem, tid);
         }
       }
+      if constexpr (has_block_flush<K>::value)
+        for (int tid = 0; tid < K::kThreads; ++tid) k.block_flush(smem, tid);
     }
   } else {
     for (long block = 0; block < grid; ++block) {

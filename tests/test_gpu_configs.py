@@ -60,6 +60,54 @@ def test_cfg3_ragged_segments_fbank_and_acoustic(fe):
         _acoustic_close(list(f.values()), list(ref.values()))
 
 
+def test_cfg3_full_size_4096_segments(fe):
+    """cfg3 at BASELINE size: 4 096 mono segments of 0.5-30 s (the lengths of synth.cfg3_segments, seed 7, incl. the
+    forced edge lengths 8 000 / 8 001 / 16 000 / 479 999 / 480 000).  Properties on everything -- batch order, padded
+    lengths, masks, finiteness, tempo's closed form -- and oracle parity on the first, a middle and the last batch of
+    16 and on eight sampled acoustic rows.  The waveforms are speech-like for the sampled ones and seeded device noise
+    for the rest (synthesising 17 hours of speech-like audio on one host core would take minutes)."""
+    import torch
+    from audio_processor_b200 import SpeechSegment, synth
+    from audio_processor_b200.acoustic import TEMPO_SLOT, _tempo
+    n_seg, sr = 4096, 16000
+    u = torch.rand(n_seg, generator=torch.Generator().manual_seed(7), dtype=torch.float64)
+    lens = list(synth.CFG3_EDGE_LENGTHS) + [int(sr * (0.5 + 29.5 * float(v))) for v in u][:n_seg - len(synth.CFG3_EDGE_LENGTHS)]
+    order = sorted(range(n_seg), key=lens.__getitem__)
+    sampled_groups = (0, 128, 255)
+    sampled = {i for g in sampled_groups for i in order[16 * g:16 * g + 16]}
+    gen = torch.Generator(device=fe.device).manual_seed(77)
+    segs = []
+    for i, n in enumerate(lens):
+        if i in sampled:
+            segs.append(synth.speech_like(n, sr, 1000 + i).to(fe.device).unsqueeze(0))
+        else:
+            segs.append(((torch.rand(n, generator=gen, device=fe.device) - 0.5) * 0.6).unsqueeze(0))
+    seg = SpeechSegment({"gpu_index": 0, "batch_size": 16})
+    items = [{"segment_waveform": s, "start": 0.0, "end": n / sr, "speaker": "client"} for s, n in zip(segs, lens)]
+    groups = seg.featurise_segments(items, sr)
+    assert len(groups) == 256 and [i for idxs, _, _ in groups for i in idxs] == order
+    for g, (idxs, feat, mask) in enumerate(groups):
+        T = [1 + (lens[i] - 400) // 160 for i in idxs]
+        assert tuple(feat.shape) == (16, (max(T) + 1) // 2, 160)
+        assert mask.sum(1).tolist() == [t // 2 for t in T]
+        assert torch.isfinite(feat).all()
+    for g in sampled_groups:
+        idxs, feat, mask = groups[g]
+        ref_f, ref_m = np_fbank.featurise([segs[i][0].cpu().numpy() for i in idxs])
+        assert np.array_equal(mask.cpu().numpy(), ref_m)
+        _cmp_nan(feat.cpu().numpy(), ref_f, 1e-3)
+    rows, status = fe.acoustic([s[0] for s in segs], sr)
+    assert int(status.sum()) == 0 and torch.isfinite(rows).all()
+    host = rows.cpu()
+    for i in (0, 1, 4, 777, 4095):                                  # tempo: the reference's closed form, exact
+        assert _tempo(float(host[i, TEMPO_SLOT]), lens[i], sr) == 60.0 / (((1 + lens[i] // 160) - 2) * 160 / sr)
+    for i in sorted(sampled)[::6]:
+        ref = np_acoustic.acoustic_features(segs[i][0].cpu().numpy())
+        vals = host[i].tolist()
+        vals[TEMPO_SLOT] = _tempo(vals[TEMPO_SLOT], lens[i], sr)
+        _acoustic_close(vals, list(ref.values()))
+
+
 # ------------------------------------------------------------------ cfg5: 44.1 kHz long form
 def test_cfg5_44k_resample_chunks_and_long_fbank(fe):
     import torch
