@@ -344,9 +344,6 @@ template <typename T> struct FbankPipeKernel {
 #ifndef AFE_PIPE_LAG
 #define AFE_PIPE_LAG 2         // AUX runs the statistics + store of tile j - AFE_PIPE_LAG after the pre-emphasis pass of tile j
 #endif
-#ifndef AFE_PIPE_SKIP
-#define AFE_PIPE_SKIP 0        // lab only (tools/kernel_lab.py): bit 0 / 1 / 2 drops the work of S1 / S2 / AUX, the hand-overs stay
-#endif
 #if AFE_CUDA
 // named barriers (ids 1..15; id 0 is __syncthreads)
 __device__ __forceinline__ void nbar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
@@ -410,10 +407,10 @@ __global__ void __launch_bounds__(K::kThreads, 1) fbank_pipe_kernel(const K k, u
     for (long t = first; t < end; ++t) {
       R r[25], c;
       tick(); nbar_sync(kBarDFull, kPair); tock(0);
-      if (!(AFE_PIPE_SKIP & 1)) k.stage1_load(afe_smem, g, r, c);
+      k.stage1_load(afe_smem, g, r, c);
       if (t + 1 < end) nbar_arrive(kBarDEmpty, kPair);
       tick(); if (t > first) nbar_sync(kBarXEmpty, kPair); tock(1);
-      if (!(AFE_PIPE_SKIP & 1)) k.stage1_compute(afe_smem, g, r, c);
+      k.stage1_compute(afe_smem, g, r, c);
       nbar_arrive(kBarXFull, kPair);
     }
   } else if (grp == 1) {
@@ -422,12 +419,12 @@ __global__ void __launch_bounds__(K::kThreads, 1) fbank_pipe_kernel(const K k, u
       const int ob = (int)(t & 1);
       cplx<R> v[16];
       tick(); nbar_sync(kBarXFull, kPair); tock(0);
-      if (!(AFE_PIPE_SKIP & 2)) k.stage2_load(afe_smem, g, v);
+      k.stage2_load(afe_smem, g, v);
       if (t + 1 < end) nbar_arrive(kBarXEmpty, kPair);
-      if (!(AFE_PIPE_SKIP & 2)) k.stage2_compute(afe_smem, g, v);
+      k.stage2_compute(afe_smem, g, v);
       nbar_sync(kBarS2, kG);                                 // sP complete
       tick(); if (t >= first + 2) nbar_sync(kBarOEmpty + ob, kPair); tock(1);
-      if (!(AFE_PIPE_SKIP & 2)) k.mel(ob, afe_smem, g);
+      k.mel(ob, afe_smem, g);
       nbar_arrive(kBarOFull + ob, kPair);
       nbar_sync(kBarS2, kG);                                 // sP read: the next tile's stage 2 may overwrite it
     }
@@ -443,14 +440,14 @@ __global__ void __launch_bounds__(K::kThreads, 1) fbank_pipe_kernel(const K k, u
         else { k.pre_copy(it, rb, afe_smem, g); nbar_sync(kBarAux, kG); }
         tock(0);
         tick(); if (j > first) nbar_sync(kBarDEmpty, kPair); tock(1);
-        if (!(AFE_PIPE_SKIP & 4)) k.pre_a(it, rb, afe_smem, g);
+        k.pre_a(it, rb, afe_smem, g);
         nbar_sync(kBarAux, kG);
         if (lead && j + 2 < end) {          // raw[rb] is free: stage tile j + 2
           const Item nx = k.next(items[(j + 1) % kRing], j + 2);
           items[(j + 2) % kRing] = nx;
           issue(nx, rb);
         }
-        if (!(AFE_PIPE_SKIP & 4)) k.pre_b(afe_smem, g);
+        k.pre_b(afe_smem, g);
         nbar_arrive(kBarDFull, kPair);
       }
       const long u = j - kLag;
@@ -458,9 +455,9 @@ __global__ void __launch_bounds__(K::kThreads, 1) fbank_pipe_kernel(const K k, u
         const Item& iu = items[u % kRing];
         const int ob = (int)(u & 1);
         tick(); nbar_sync(kBarOFull + ob, kPair); tock(2);
-        if (!(AFE_PIPE_SKIP & 4)) k.stats_store(iu, ob, afe_smem, g);
+        k.stats_store(iu, ob, afe_smem, g);
         if (u + 2 < end) nbar_arrive(kBarOEmpty + ob, kPair);
-        if (!(AFE_PIPE_SKIP & 4) && k.tail(iu)) {
+        if (k.tail(iu)) {
           tick();
           nbar_sync(kBarAux, kG);           // stat[] complete
           k.tail_norm(iu, afe_smem, g);
